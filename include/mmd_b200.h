@@ -1,0 +1,90 @@
+/* C ABI of the B200 searchlight ridge-decoding engine (libmmd_b200.so).
+ *
+ * The reference (mitjanikolaus/multimodal_decoding) is pure Python and has no FFI layer; its
+ * boundary for this path is a set of Python functions.  Each entry point below names the reference
+ * function whose work it takes over; the Python mirror of those functions
+ * (multimodal_decoding_b200/analyses/decoding/searchlight/searchlight.py) binds them with ctypes,
+ * see INTEGRATION.md.  Paths are relative to the reference root.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every data pointer may be a HOST pointer or a DEVICE pointer on
+ *     the handle's GPU (detected with cudaPointerGetAttributes); host buffers are copied by the
+ *     library, device buffers are borrowed for the duration of the call;
+ *   - every function returns 0 on success; on failure a non-zero code is returned and
+ *     mmd_last_error() describes it (CUDA error string or argument error);
+ *   - a handle owns one CUDA stream and its workspaces; handles are independent, one handle must not
+ *     be used from two threads at once;
+ *   - there is no CPU fallback: without a usable CUDA device mmd_create fails.
+ */
+#ifndef MMD_B200_H
+#define MMD_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mmd_handle mmd_handle;
+
+#define MMD_N_SCORES 8          /* order: see MMD_SCORE_NAMES in mmd_score_name() */
+#define MMD_EVAL_PAD 144        /* test + imagery trials per centre must be <= 143 */
+
+/* Number of stage timers reported by mmd_get_stats (pack, xty, prep, syrk, factor_solve, predict, score, knn). */
+#define MMD_N_STAGES 8
+
+int mmd_create(int device, mmd_handle** out);
+void mmd_destroy(mmd_handle* h);
+const char* mmd_last_error(const mmd_handle* h);
+const char* mmd_version(void);
+
+/* Name of score column i (0..7), e.g. "pairwise_acc_captions"; eval.py:9-44 and searchlight.py:87. */
+const char* mmd_score_name(int i);
+
+/* Replaces the k-NN branch of get_adjacency_matrix (analyses/decoding/searchlight/searchlight.py:152-178,
+ * i.e. sklearn NearestNeighbors().fit(coords).kneighbors(coords, k)).
+ *   coords      (n_vertices x 3) float64
+ *   queries     rows q_begin .. q_end-1 of coords
+ *   idx_out     ((q_end-q_begin) x k) int64, ascending distance, the query itself first
+ *   dist_out    ((q_end-q_begin) x k) float64 Euclidean distances */
+int mmd_knn(mmd_handle* h, const double* coords, int n_vertices, int k, int q_begin, int q_end,
+            int64_t* idx_out, double* dist_out);
+
+/* Stages the arrays custom_search_light receives (searchlight.py:117-129; built at :217-248) on the GPU.
+ *   X            (n_total x n_vertices) float16 row-major, trials x vertices
+ *   Y            (n_total x n_dims)     float16 row-major, trials x embedding dims
+ *   train_ids / test_ids / imagery_ids  row indices into X and Y (searchlight.py:229-232)
+ *   test_is_caption[n_test]             1 where TEST_STIM_TYPES == "caption" (data.py:182-187), else 0
+ * Builds the vertex-major panels and X_train^T Y_train once (used by every centre). */
+int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
+               const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
+               const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery);
+
+/* Replaces the loop of custom_group_iter_search_light + train_and_test (searchlight.py:38-114) for
+ * `n_centres` centres with a fixed neighbourhood size k: ridge fit with `alpha`
+ * (Ridge(alpha, fit_intercept=False), searchlight.py:240), prediction of the test and imagery trials and
+ * the 8 pairwise-accuracy scores (eval.py:126-181).
+ *   adjacency    (n_centres x k) int32 vertex ids (columns of X), HOST pointer
+ *   scores_out   (n_centres x 8) float64, HOST or DEVICE
+ *   flags_out    (n_centres) int32, 1 where the normal matrix was not positive definite; may be NULL */
+int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
+                    double* scores_out, int32_t* flags_out);
+
+/* Test/diagnostic hook: predictions of one centre, (143 x n_dims) float64 in the internal row order
+ * [caption test trials, image test trials, imagery trials]; HOST pointer. */
+int mmd_predict_centre(mmd_handle* h, const int32_t* neighbours, int k, double alpha, double* yhat_out);
+
+/* Cumulative GPU time per stage in milliseconds (CUDA events on the handle's stream) and the number of
+ * kernel launches since the last mmd_reset_stats. */
+int mmd_get_stats(mmd_handle* h, float stage_ms[MMD_N_STAGES], int64_t* n_launches, int64_t* n_clusters,
+                  double* syrk_flops);
+void mmd_reset_stats(mmd_handle* h);
+const char* mmd_stage_name(int i);
+
+/* Tuning knobs (0 keeps the default): centres per cluster, max centres per batch. */
+int mmd_configure(mmd_handle* h, int cluster_size, int batch_centres, int host_threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MMD_B200_H */

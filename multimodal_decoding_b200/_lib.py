@@ -1,0 +1,57 @@
+"""ctypes binding of the C ABI declared in include/mmd_b200.h (libmmd_b200.so, built in-tree)."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmmd_b200.so")
+
+N_SCORES = 8
+N_STAGES = 8
+EVAL_PAD = 144
+
+EXPORTS = [
+    "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_upload",
+    "mmd_searchlight", "mmd_predict_centre", "mmd_get_stats", "mmd_reset_stats", "mmd_stage_name", "mmd_configure",
+]
+
+_lib = None
+
+
+def load():
+    """Load the shared library; raises if it has not been built (there is no fallback path)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -m multimodal_decoding_b200.build` "
+            "(the searchlight has no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, ip, i32, i64, dbl = C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.c_int64, C.c_double
+    lib.mmd_create.argtypes = [i32, C.POINTER(vp)]
+    lib.mmd_create.restype = i32
+    lib.mmd_destroy.argtypes = [vp]
+    lib.mmd_destroy.restype = None
+    lib.mmd_last_error.argtypes = [vp]
+    lib.mmd_last_error.restype = C.c_char_p
+    lib.mmd_version.restype = C.c_char_p
+    lib.mmd_score_name.argtypes = [i32]
+    lib.mmd_score_name.restype = C.c_char_p
+    lib.mmd_stage_name.argtypes = [i32]
+    lib.mmd_stage_name.restype = C.c_char_p
+    lib.mmd_knn.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp]
+    lib.mmd_knn.restype = i32
+    lib.mmd_upload.argtypes = [vp, vp, i32, i32, vp, i32, vp, i32, vp, i32, vp, vp, i32]
+    lib.mmd_upload.restype = i32
+    lib.mmd_searchlight.argtypes = [vp, vp, i32, i32, dbl, vp, vp]
+    lib.mmd_searchlight.restype = i32
+    lib.mmd_predict_centre.argtypes = [vp, vp, i32, dbl, vp]
+    lib.mmd_predict_centre.restype = i32
+    lib.mmd_get_stats.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i64), C.POINTER(i64), C.POINTER(dbl)]
+    lib.mmd_get_stats.restype = i32
+    lib.mmd_reset_stats.argtypes = [vp]
+    lib.mmd_reset_stats.restype = None
+    lib.mmd_configure.argtypes = [vp, i32, i32, i32]
+    lib.mmd_configure.restype = i32
+    _lib = lib
+    return lib

@@ -1,0 +1,667 @@
+// C ABI (include/mmd_b200.h) and host orchestration of the searchlight engine.
+//
+// Host-side work that has no counterpart in the reference: centres are grouped into spatial clusters so
+// that the float64 Gram of a cluster's neighbourhood *union* is computed once (symmetric rank-k update on
+// the DMMA pipe) and every member centre reads its k x k normal matrix as a sub-matrix of it.  For the
+// reference's k-NN adjacency (searchlight.py:173) a 128-centre cluster has a union of ~2k vertices, which
+// cuts the Gram work per centre from 2*N*k^2 to ~2*N*u^2/(2*128) (reported as executed flops).
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/mmd_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+
+using namespace mmd;
+
+namespace {
+
+enum Stage { ST_PACK = 0, ST_XTY, ST_PREP, ST_SYRK, ST_SOLVE, ST_PREDICT, ST_SCORE, ST_KNN };
+const char* kStageNames[MMD_N_STAGES] = {"pack", "xty", "prep", "syrk", "factor_solve", "predict", "score", "knn"};
+const char* kScoreNames[MMD_N_SCORES] = {
+    "pairwise_acc_captions",
+    "pairwise_acc_images",
+    "pairwise_acc_cross_captions_to_images",
+    "pairwise_acc_cross_images_to_captions",
+    "pairwise_acc_imagery",
+    "pairwise_acc_imagery_whole_test_set",
+    "pairwise_acc_imagery_no_std",
+    "pairwise_acc_imagery_whole_test_set_no_std",
+};
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t need) {
+        if (need <= bytes) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMalloc(&p, need);
+        if (e == cudaSuccess) bytes = need;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <typename T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct TimedSpan {
+    cudaEvent_t a, b;
+    int stage;
+};
+
+}  // namespace
+
+struct mmd_handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    // uploaded problem
+    int V = 0, n_train = 0, ldt = 0, n_test = 0, n_cap = 0, n_img = 0, n_im = 0, D = 0, Dp = 0;
+    bool uploaded = false;
+    DevBuf Xt, Xe, Yt, cand, cand_sq, XtY;
+    // per-call / per-batch workspaces
+    DevBuf adj, union_vertices, task_row, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
+        work, yhat, scores, flags, misc_flag, tmp;
+    // knobs
+    int cluster_size = 128, batch_centres = 2048, host_threads = 0;
+    // stats
+    float stage_ms[MMD_N_STAGES] = {0};
+    int64_t launches = 0, n_clusters = 0;
+    double syrk_flops = 0.0;
+    std::vector<cudaEvent_t> event_pool;
+    size_t events_used = 0;
+    std::vector<TimedSpan> spans;
+};
+
+namespace {
+
+int fail(mmd_handle* h, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (h) h->err = buf;
+    return 1;
+}
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess) return fail(h, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                                            __FILE__, __LINE__);                                         \
+    } while (0)
+
+bool is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+cudaEvent_t next_event(mmd_handle* h) {
+    if (h->events_used == h->event_pool.size()) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        h->event_pool.push_back(e);
+    }
+    return h->event_pool[h->events_used++];
+}
+void span_begin(mmd_handle* h, int stage) {
+    TimedSpan s{next_event(h), next_event(h), stage};
+    cudaEventRecord(s.a, h->stream);
+    h->spans.push_back(s);
+}
+void span_end(mmd_handle* h, int n_launches = 1) {
+    cudaEventRecord(h->spans.back().b, h->stream);
+    h->launches += n_launches;
+}
+// call after the stream is synchronised
+void resolve_spans(mmd_handle* h) {
+    for (auto& s : h->spans) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) h->stage_ms[s.stage] += ms;
+    }
+    h->spans.clear();
+    h->events_used = 0;
+    cudaGetLastError();
+}
+
+template <typename T>
+int to_device(mmd_handle* h, DevBuf& buf, const T* src, size_t n) {
+    CU(buf.ensure(std::max<size_t>(n, 1) * sizeof(T)));
+    if (n) CU(cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyDefault, h->stream));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// host plan: spatial clusters of centres and the sorted union of their neighbourhoods
+// ------------------------------------------------------------------------------------------
+struct Plan {
+    std::vector<int> cl_off;      // cluster c owns members[cl_off[c] .. cl_off[c+1])
+    std::vector<int> members;     // centre (adjacency row) indices
+    std::vector<long> un_off;     // union of cluster c = un_vert[un_off[c] .. un_off[c+1])
+    std::vector<int> un_vert;     // ascending vertex ids
+};
+
+void build_plan(const int32_t* adj, int n_centres, int k, int V, int cluster_size, int n_threads, Plan& plan) {
+    // greedy region growing: a seed takes its nearest still-unassigned centres (adjacency rows are ordered
+    // by distance in the reference, the centre itself first)
+    std::vector<int> centre_of(V, -1);
+    for (int i = n_centres - 1; i >= 0; --i) {
+        const int v = adj[(long)i * k];
+        if (v >= 0 && v < V) centre_of[v] = i;
+    }
+    std::vector<char> assigned(n_centres, 0);
+    const int reach = std::min(k, 3 * cluster_size);
+    plan.cl_off.assign(1, 0);
+    plan.members.clear();
+    plan.members.reserve(n_centres);
+    for (int s = 0; s < n_centres; ++s) {
+        if (assigned[s]) continue;
+        assigned[s] = 1;
+        plan.members.push_back(s);
+        int count = 1;
+        const int32_t* row = adj + (long)s * k;
+        for (int j = 0; j < reach && count < cluster_size; ++j) {
+            const int v = row[j];
+            if (v < 0 || v >= V) continue;
+            const int c = centre_of[v];
+            if (c >= 0 && !assigned[c]) {
+                assigned[c] = 1;
+                plan.members.push_back(c);
+                ++count;
+            }
+        }
+        plan.cl_off.push_back((int)plan.members.size());
+    }
+    const int n_clusters = (int)plan.cl_off.size() - 1;
+    // unions, in parallel over clusters
+    std::vector<std::vector<int>> unions(n_clusters);
+    n_threads = std::max(1, std::min(n_threads, n_clusters));
+    std::atomic<int> next(0);
+    auto worker = [&]() {
+        std::vector<int> stamp(V, -1);
+        for (;;) {
+            const int c = next.fetch_add(1);
+            if (c >= n_clusters) break;
+            std::vector<int>& u = unions[c];
+            for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) {
+                const int32_t* row = adj + (long)plan.members[m] * k;
+                for (int j = 0; j < k; ++j) {
+                    const int v = row[j];
+                    if (v < 0 || v >= V) continue;       // reported by the device-side check
+                    if (stamp[v] != c) {
+                        stamp[v] = c;
+                        u.push_back(v);
+                    }
+                }
+            }
+            std::sort(u.begin(), u.end());
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < n_threads; ++t) pool.emplace_back(worker);
+    worker();
+    for (auto& t : pool) t.join();
+    plan.un_off.assign(1, 0);
+    size_t total = 0;
+    for (auto& u : unions) total += u.size();
+    plan.un_vert.clear();
+    plan.un_vert.reserve(total);
+    for (auto& u : unions) {
+        plan.un_vert.insert(plan.un_vert.end(), u.begin(), u.end());
+        plan.un_off.push_back((long)plan.un_vert.size());
+    }
+}
+
+int run_xty(mmd_handle* h) {
+    GemmProblem p{};
+    p.A = h->Xt.as<__half>();
+    p.lda = h->ldt;
+    p.rowsA = nullptr;
+    p.M = h->V;
+    p.B = h->Yt.as<__half>();
+    p.ldb = h->ldt;
+    p.rowsB = nullptr;
+    p.N = h->Dp;
+    p.K = h->ldt;
+    p.C = h->XtY.as<double>();
+    p.ldc = h->Dp;
+    p.lower_only = 0;
+    if (to_device(h, h->probs, &p, 1)) return 1;
+    span_begin(h, ST_XTY);
+    CU(launch_gemm_gather(h->probs.as<GemmProblem>(), 1, p.M, p.N, h->stream));
+    span_end(h);
+    return 0;
+}
+
+// One batch = clusters [c0, c1).  `slot0` = first output slot when yhat_only (diagnostic) is set.
+int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, double alpha) {
+    const int n_cl = c1 - c0;
+    const int t0 = plan.cl_off[c0], n_tasks = plan.cl_off[c1] - t0;
+    std::vector<int> task_row(n_tasks), task_un_n(n_tasks);
+    std::vector<long> task_un_off(n_tasks);
+    std::vector<CentreTask> tasks(n_tasks);
+    std::vector<GemmProblem> probs(n_cl);
+    size_t pool_doubles = 0;
+    int max_u = 0;
+    for (int c = c0; c < c1; ++c) {
+        const int u = (int)(plan.un_off[c + 1] - plan.un_off[c]);
+        const long ldu = round_up(u, 8);
+        GemmProblem& p = probs[c - c0];
+        p.A = p.B = h->Xt.as<__half>();
+        p.lda = p.ldb = h->ldt;
+        p.rowsA = p.rowsB = h->union_vertices.as<int>() + plan.un_off[c];
+        p.M = p.N = u;
+        p.K = h->ldt;
+        p.C = h->gram_pool.as<double>() + pool_doubles;     // pool base fixed before this call
+        p.ldc = ldu;
+        p.lower_only = 1;
+        for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) {
+            const int t = m - t0;
+            task_row[t] = plan.members[m];
+            task_un_off[t] = plan.un_off[c];
+            task_un_n[t] = u;
+            CentreTask& ct = tasks[t];
+            ct.gram = p.C;
+            ct.gram_ld = ldu;
+            ct.loc = h->loc.as<int>() + (long)t * kp;
+            ct.nbr = h->nbr_sorted.as<int>() + (long)t * kp;
+            ct.centre = plan.members[m];
+        }
+        pool_doubles += (size_t)u * ldu;
+        max_u = std::max(max_u, u);
+        // executed flops of the lower-triangular 128 x 64 tiles
+        const long tm = (u + 127) / 128;
+        long tiles = 0;
+        for (long i = 0; i < tm; ++i) tiles += std::min<long>((i * 128 + 127) / 64 + 1, (u + 63) / 64);
+        h->syrk_flops += 2.0 * tiles * 128.0 * 64.0 * h->ldt;
+    }
+    if (pool_doubles * sizeof(double) > h->gram_pool.bytes) return fail(h, "internal: gram pool too small");
+    if (to_device(h, h->task_row, task_row.data(), n_tasks)) return 1;
+    if (to_device(h, h->task_union_off, task_un_off.data(), n_tasks)) return 1;
+    if (to_device(h, h->task_union_n, task_un_n.data(), n_tasks)) return 1;
+    if (to_device(h, h->tasks, tasks.data(), n_tasks)) return 1;
+    if (to_device(h, h->probs, probs.data(), n_cl)) return 1;
+
+    span_begin(h, ST_PREP);
+    CU(launch_prep_tasks(h->adj.as<int>(), k, kp, h->task_row.as<int>(), h->task_union_off.as<long>(),
+                         h->task_union_n.as<int>(), h->union_vertices.as<int>(), h->V, n_tasks,
+                         h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
+    span_end(h);
+
+    span_begin(h, ST_SYRK);
+    CU(launch_gemm_gather(h->probs.as<GemmProblem>(), n_cl, max_u, max_u, h->stream));
+    span_end(h);
+
+    SolveParams sp{};
+    sp.tasks = h->tasks.as<CentreTask>();
+    sp.n_tasks = n_tasks;
+    sp.k = k;
+    sp.kp = kp;
+    sp.alpha = alpha;
+    sp.Xe = h->Xe.as<__half>();
+    sp.work = h->work.as<double>();
+    sp.flags = h->flags.as<int>();
+    span_begin(h, ST_SOLVE);
+    CU(launch_factor_solve(sp, h->stream));
+    span_end(h);
+
+    PredictParams pp{};
+    pp.tasks = sp.tasks;
+    pp.n_tasks = n_tasks;
+    pp.k = k;
+    pp.kp = kp;
+    pp.work = h->work.as<double>();
+    pp.XtY = h->XtY.as<double>();
+    pp.Dp = h->Dp;
+    pp.yhat = h->yhat.as<double>();
+    span_begin(h, ST_PREDICT);
+    CU(launch_predict(pp, h->stream));
+    span_end(h);
+
+    ScoreParams sc{};
+    sc.tasks = sp.tasks;
+    sc.n_tasks = n_tasks;
+    sc.yhat = h->yhat.as<double>();
+    sc.Dp = h->Dp;
+    sc.cand = h->cand.as<__half>();
+    sc.cand_sq = h->cand_sq.as<double>();
+    sc.n_cap = h->n_cap;
+    sc.n_img = h->n_img;
+    sc.n_im = h->n_im;
+    sc.scores = h->scores.as<double>();
+    span_begin(h, ST_SCORE);
+    CU(launch_score(sc, h->stream));
+    span_end(h);
+    return 0;
+}
+
+int run_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha) {
+    if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight");
+    if (k < 1 || k > h->V) return fail(h, "k=%d out of range (1..%d)", k, h->V);
+    if (k > h->n_train)
+        return fail(h, "k=%d exceeds n_train=%d: the primal normal equations are rank deficient only through "
+                       "alpha; the dual form is not implemented on this path", k, h->n_train);
+    if (k > 2000) return fail(h, "k=%d exceeds the supported maximum of 2000", k);
+    const int kp = round_up(k, NB);
+    int n_threads = h->host_threads > 0 ? h->host_threads : (int)std::thread::hardware_concurrency();
+    n_threads = std::max(1, std::min(n_threads, 32));
+
+    if (to_device(h, h->adj, adjacency, (size_t)n_centres * k)) return 1;
+    Plan plan;
+    build_plan(adjacency, n_centres, k, h->V, h->cluster_size, n_threads, plan);
+    const int n_clusters = (int)plan.cl_off.size() - 1;
+    h->n_clusters += n_clusters;
+    if (to_device(h, h->union_vertices, plan.un_vert.data(), plan.un_vert.size())) return 1;
+
+    // batches: whole clusters, at most batch_centres centres
+    std::vector<int> batch_start(1, 0);
+    size_t max_pool = 0, cur_pool = 0;
+    int cur_tasks = 0, max_tasks = 0;
+    for (int c = 0; c < n_clusters; ++c) {
+        const int m = plan.cl_off[c + 1] - plan.cl_off[c];
+        const size_t u = (size_t)(plan.un_off[c + 1] - plan.un_off[c]);
+        const size_t g = u * round_up((int)u, 8);
+        if (cur_tasks > 0 && cur_tasks + m > h->batch_centres) {
+            batch_start.push_back(c);
+            cur_tasks = 0;
+            cur_pool = 0;
+        }
+        cur_tasks += m;
+        cur_pool += g;
+        max_tasks = std::max(max_tasks, cur_tasks);
+        max_pool = std::max(max_pool, cur_pool);
+    }
+    batch_start.push_back(n_clusters);
+
+    CU(h->gram_pool.ensure(max_pool * sizeof(double)));
+    CU(h->work.ensure((size_t)max_tasks * (kp + EVAL_PAD) * kp * sizeof(double)));
+    CU(h->yhat.ensure((size_t)max_tasks * EVAL_PAD * h->Dp * sizeof(double)));
+    CU(h->nbr_sorted.ensure((size_t)max_tasks * kp * sizeof(int)));
+    CU(h->loc.ensure((size_t)max_tasks * kp * sizeof(int)));
+    CU(h->scores.ensure((size_t)n_centres * MMD_N_SCORES * sizeof(double)));
+    CU(h->flags.ensure((size_t)n_centres * sizeof(int)));
+    CU(h->misc_flag.ensure(sizeof(int)));
+    CU(cudaMemsetAsync(h->misc_flag.p, 0, sizeof(int), h->stream));
+    CU(cudaMemsetAsync(h->flags.p, 0, (size_t)n_centres * sizeof(int), h->stream));
+
+    for (size_t b = 0; b + 1 < batch_start.size(); ++b)
+        if (run_batch(h, plan, batch_start[b], batch_start[b + 1], k, kp, alpha)) return 1;
+    return 0;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// exported functions
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* mmd_version(void) { return "mmd_b200 0.1 (sm_100a)"; }
+const char* mmd_score_name(int i) { return (i >= 0 && i < MMD_N_SCORES) ? kScoreNames[i] : ""; }
+const char* mmd_stage_name(int i) { return (i >= 0 && i < MMD_N_STAGES) ? kStageNames[i] : ""; }
+
+int mmd_create(int device, mmd_handle** out) {
+    if (!out) return 1;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) return 2;
+    if (cudaSetDevice(device) != cudaSuccess) return 3;
+    mmd_handle* h = new mmd_handle();
+    h->device = device;
+    if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete h;
+        return 4;
+    }
+    *out = h;
+    return 0;
+}
+
+void mmd_destroy(mmd_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
+                      &h->task_row, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
+                      &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp};
+    for (DevBuf* b : bufs) b->release();
+    for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
+    cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+const char* mmd_last_error(const mmd_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+int mmd_configure(mmd_handle* h, int cluster_size, int batch_centres, int host_threads) {
+    if (!h) return 1;
+    if (cluster_size > 0) h->cluster_size = cluster_size;
+    if (batch_centres > 0) h->batch_centres = batch_centres;
+    if (host_threads > 0) h->host_threads = host_threads;
+    return 0;
+}
+
+void mmd_reset_stats(mmd_handle* h) {
+    if (!h) return;
+    memset(h->stage_ms, 0, sizeof(h->stage_ms));
+    h->launches = 0;
+    h->n_clusters = 0;
+    h->syrk_flops = 0.0;
+}
+
+int mmd_get_stats(mmd_handle* h, float stage_ms[MMD_N_STAGES], int64_t* n_launches, int64_t* n_clusters,
+                  double* syrk_flops) {
+    if (!h) return 1;
+    if (stage_ms) memcpy(stage_ms, h->stage_ms, sizeof(h->stage_ms));
+    if (n_launches) *n_launches = h->launches;
+    if (n_clusters) *n_clusters = h->n_clusters;
+    if (syrk_flops) *syrk_flops = h->syrk_flops;
+    return 0;
+}
+
+int mmd_knn(mmd_handle* h, const double* coords, int n_vertices, int k, int q_begin, int q_end, int64_t* idx_out,
+            double* dist_out) {
+    if (!h) return 1;
+    if (!coords || !idx_out || !dist_out) return fail(h, "mmd_knn: null pointer");
+    if (q_begin < 0 || q_end > n_vertices || q_begin > q_end) return fail(h, "mmd_knn: bad query range");
+    if (k < 1 || k > n_vertices || k > 2000) return fail(h, "mmd_knn: k=%d out of range", k);
+    CU(cudaSetDevice(h->device));
+    const size_t nq = (size_t)(q_end - q_begin);
+    DevBuf dcoords, didx, ddist;
+    const double* c_dev = coords;
+    int rc = 0;
+    do {
+        if (!is_device_ptr(coords)) {
+            if (dcoords.ensure((size_t)n_vertices * 3 * sizeof(double)) != cudaSuccess) { rc = fail(h, "mmd_knn: out of memory"); break; }
+            cudaMemcpyAsync(dcoords.p, coords, (size_t)n_vertices * 3 * sizeof(double), cudaMemcpyHostToDevice, h->stream);
+            c_dev = dcoords.as<double>();
+        }
+        int64_t* i_dev = idx_out;
+        double* d_dev = dist_out;
+        const bool idx_host = !is_device_ptr(idx_out), dist_host = !is_device_ptr(dist_out);
+        if (idx_host) {
+            if (didx.ensure(std::max<size_t>(nq * k, 1) * sizeof(int64_t)) != cudaSuccess) { rc = fail(h, "mmd_knn: out of memory"); break; }
+            i_dev = didx.as<int64_t>();
+        }
+        if (dist_host) {
+            if (ddist.ensure(std::max<size_t>(nq * k, 1) * sizeof(double)) != cudaSuccess) { rc = fail(h, "mmd_knn: out of memory"); break; }
+            d_dev = ddist.as<double>();
+        }
+        if (h->misc_flag.ensure(sizeof(int)) != cudaSuccess) { rc = fail(h, "mmd_knn: out of memory"); break; }
+        cudaMemsetAsync(h->misc_flag.p, 0, sizeof(int), h->stream);
+        span_begin(h, ST_KNN);
+        cudaError_t e = launch_knn(c_dev, n_vertices, k, q_begin, q_end, i_dev, d_dev, h->misc_flag.as<int>(), h->stream);
+        span_end(h);
+        if (e != cudaSuccess) { rc = fail(h, "knn launch failed: %s", cudaGetErrorString(e)); break; }
+        int flag = 0;
+        cudaMemcpyAsync(&flag, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream);
+        if (idx_host) cudaMemcpyAsync(idx_out, i_dev, nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream);
+        if (dist_host) cudaMemcpyAsync(dist_out, d_dev, nq * k * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+        e = cudaStreamSynchronize(h->stream);
+        resolve_spans(h);
+        if (e != cudaSuccess) { rc = fail(h, "mmd_knn failed: %s", cudaGetErrorString(e)); break; }
+        if (flag) { rc = fail(h, "mmd_knn: more than 2048 candidates tie at the k-th distance (degenerate coordinates)"); break; }
+    } while (0);
+    dcoords.release();
+    didx.release();
+    ddist.release();
+    return rc;
+}
+
+int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
+               const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
+               const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery) {
+    if (!h) return 1;
+    if (!X || !Y || !train_ids || (n_test > 0 && (!test_ids || !test_is_caption)) || (n_imagery > 0 && !imagery_ids))
+        return fail(h, "mmd_upload: null pointer");
+    if (n_total < 1 || n_vertices < 1 || n_dims < 1 || n_train < 1) return fail(h, "mmd_upload: empty input");
+    if (n_test + n_imagery > MMD_EVAL_PAD - 1)
+        return fail(h, "mmd_upload: %d test + %d imagery trials exceed the supported %d", n_test, n_imagery,
+                    MMD_EVAL_PAD - 1);
+    if (n_imagery > 8) return fail(h, "mmd_upload: at most 8 imagery trials are supported");
+    auto in_range = [&](const int32_t* ids, int n) {
+        for (int i = 0; i < n; ++i)
+            if (ids[i] < 0 || ids[i] >= n_total) return false;
+        return true;
+    };
+    if (!in_range(train_ids, n_train) || !in_range(test_ids, n_test) || !in_range(imagery_ids, n_imagery))
+        return fail(h, "mmd_upload: trial index out of range");
+    CU(cudaSetDevice(h->device));
+    h->uploaded = false;
+    h->V = n_vertices;
+    h->n_train = n_train;
+    h->ldt = round_up(n_train, 64);
+    h->n_test = n_test;
+    h->n_im = n_imagery;
+    h->D = n_dims;
+    h->Dp = round_up(n_dims, 64);
+    // evaluation rows in the internal order: captions, images, imagery
+    std::vector<int> eval_ids;
+    h->n_cap = 0;
+    for (int i = 0; i < n_test; ++i)
+        if (test_is_caption[i]) { eval_ids.push_back(test_ids[i]); ++h->n_cap; }
+    for (int i = 0; i < n_test; ++i)
+        if (!test_is_caption[i]) eval_ids.push_back(test_ids[i]);
+    h->n_img = n_test - h->n_cap;
+    for (int i = 0; i < n_imagery; ++i) eval_ids.push_back(imagery_ids[i]);
+    const int n_eval = (int)eval_ids.size();
+
+    DevBuf xtmp, ytmp, d_train, d_eval;
+    int rc = 0;
+    do {
+        const __half* Xd = reinterpret_cast<const __half*>(X);
+        const __half* Yd = reinterpret_cast<const __half*>(Y);
+        if (!is_device_ptr(X)) {
+            if ((rc = to_device(h, xtmp, reinterpret_cast<const __half*>(X), (size_t)n_total * n_vertices))) break;
+            Xd = xtmp.as<__half>();
+        }
+        if (!is_device_ptr(Y)) {
+            if ((rc = to_device(h, ytmp, reinterpret_cast<const __half*>(Y), (size_t)n_total * n_dims))) break;
+            Yd = ytmp.as<__half>();
+        }
+        if ((rc = to_device(h, d_train, train_ids, n_train))) break;
+        if ((rc = to_device(h, d_eval, eval_ids.data(), n_eval))) break;
+#define CUB(call)                                                                                  \
+    {                                                                                              \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) {                                                                  \
+            rc = fail(h, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            break;                                                                                 \
+        }                                                                                          \
+    }
+        CUB(h->Xt.ensure((size_t)n_vertices * h->ldt * sizeof(__half)));
+        CUB(h->Xe.ensure((size_t)n_vertices * EVAL_PAD * sizeof(__half)));
+        CUB(h->Yt.ensure((size_t)h->Dp * h->ldt * sizeof(__half)));
+        CUB(h->cand.ensure((size_t)EVAL_PAD * h->Dp * sizeof(__half)));
+        CUB(h->cand_sq.ensure((size_t)EVAL_PAD * sizeof(double)));
+        CUB(h->XtY.ensure((size_t)n_vertices * h->Dp * sizeof(double)));
+        CUB(cudaMemsetAsync(h->Yt.p, 0, (size_t)h->Dp * h->ldt * sizeof(__half), h->stream));
+        span_begin(h, ST_PACK);
+        launch_pack_transpose(Xd, n_vertices, d_train.as<int>(), n_train, n_vertices, h->Xt.as<__half>(), h->ldt, h->stream);
+        launch_pack_transpose(Xd, n_vertices, d_eval.as<int>(), n_eval, n_vertices, h->Xe.as<__half>(), EVAL_PAD, h->stream);
+        launch_pack_transpose(Yd, n_dims, d_train.as<int>(), n_train, n_dims, h->Yt.as<__half>(), h->ldt, h->stream);
+        gather_rows_f16_kernel<<<EVAL_PAD, 256, 0, h->stream>>>(Yd, n_dims, d_eval.as<int>(), n_eval, n_dims,
+                                                               h->cand.as<__half>(), EVAL_PAD, h->Dp);
+        // squared norms of the candidate rows (identity row list = first EVAL_PAD entries of an iota)
+        {
+            std::vector<int> iota(EVAL_PAD);
+            for (int i = 0; i < EVAL_PAD; ++i) iota[i] = i;
+            if ((rc = to_device(h, h->tmp, iota.data(), EVAL_PAD))) break;
+            row_sqnorm_kernel<<<EVAL_PAD, 128, 0, h->stream>>>(h->cand.as<__half>(), h->Dp, h->tmp.as<int>(), EVAL_PAD,
+                                                              h->Dp, h->cand_sq.as<double>());
+        }
+        span_end(h, 5);
+        CUB(cudaGetLastError());
+        if ((rc = run_xty(h))) break;
+        CUB(cudaStreamSynchronize(h->stream));
+        resolve_spans(h);
+        h->uploaded = true;
+    } while (0);
+    xtmp.release();
+    ytmp.release();
+    d_train.release();
+    d_eval.release();
+    return rc;
+}
+
+int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha, double* scores_out,
+                    int32_t* flags_out) {
+    if (!h) return 1;
+    if (!adjacency || !scores_out) return fail(h, "mmd_searchlight: null pointer");
+    if (n_centres < 0) return fail(h, "mmd_searchlight: negative centre count");
+    if (n_centres == 0) return 0;
+    if (is_device_ptr(adjacency)) return fail(h, "mmd_searchlight: adjacency must be a host pointer");
+    CU(cudaSetDevice(h->device));
+    if (run_searchlight(h, adjacency, n_centres, k, alpha)) {
+        cudaStreamSynchronize(h->stream);
+        h->spans.clear();
+        h->events_used = 0;
+        return 1;
+    }
+    int bad = 0;
+    CU(cudaMemcpyAsync(&bad, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(scores_out, h->scores.p, (size_t)n_centres * MMD_N_SCORES * sizeof(double), cudaMemcpyDefault,
+                       h->stream));
+    if (flags_out)
+        CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    resolve_spans(h);
+    if (bad == 1) return fail(h, "mmd_searchlight: adjacency holds a vertex index outside [0, %d)", h->V);
+    if (bad == 2) return fail(h, "internal: neighbour missing from its cluster union");
+    return 0;
+}
+
+int mmd_predict_centre(mmd_handle* h, const int32_t* neighbours, int k, double alpha, double* yhat_out) {
+    if (!h) return 1;
+    if (!neighbours || !yhat_out) return fail(h, "mmd_predict_centre: null pointer");
+    CU(cudaSetDevice(h->device));
+    if (run_searchlight(h, neighbours, 1, k, alpha)) {
+        cudaStreamSynchronize(h->stream);
+        h->spans.clear();
+        h->events_used = 0;
+        return 1;
+    }
+    const int n_eval = h->n_test + h->n_im;
+    CU(cudaMemcpy2DAsync(yhat_out, (size_t)h->D * sizeof(double), h->yhat.p, (size_t)h->Dp * sizeof(double),
+                         (size_t)h->D * sizeof(double), n_eval, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    resolve_spans(h);
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,94 @@
+// Internal launch interface between the C-ABI (api.cu) and the kernels.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace mmd {
+
+// ---- pack.cu -----------------------------------------------------------------------------
+void launch_pack_transpose(const __half* X, long ldx, const int* ids_dev, int n_ids, int V, __half* out,
+                           int ld_out, cudaStream_t s);
+__global__ void row_sqnorm_kernel(const __half* Y, long ldy, const int* rows, int n_rows, int D, double* sq);
+
+// ---- gemm_gather.cu ----------------------------------------------------------------------
+struct GemmProblem {
+    const __half* A;
+    long lda;
+    const int* rowsA;   // optional gather list (device), nullptr = identity
+    int M;
+    const __half* B;
+    long ldb;
+    const int* rowsB;
+    int N;
+    int K;              // multiple of 64; rows are zero padded up to it
+    double* C;
+    long ldc;           // even
+    int lower_only;     // skip tiles strictly above the diagonal (symmetric rank-k update)
+};
+size_t gemm_gather_smem_bytes();
+cudaError_t launch_gemm_gather(const GemmProblem* probs_dev, int n_problems, int max_m, int max_n, cudaStream_t s);
+
+// ---- factor_solve.cu ---------------------------------------------------------------------
+// One searchlight centre = one CTA.  All pointers are device pointers.
+struct CentreTask {
+    const double* gram;   // the cluster's union Gram (lower triangle valid), row-major
+    long gram_ld;
+    const int* loc;       // k ascending positions of this centre's neighbours inside the union
+    const int* nbr;       // k vertex ids in the same (ascending) order
+    int centre;           // output slot (index into scores / flags)
+};
+struct SolveParams {
+    const CentreTask* tasks;
+    int n_tasks;
+    int k;                // neighbours per centre
+    int kp;               // k rounded up to a multiple of 64
+    double alpha;
+    const __half* Xe;     // (V x EVAL_PAD) evaluation trials per vertex
+    double* work;         // per task: (kp + EVAL_PAD) x kp doubles
+    int* flags;           // per task slot: 1 if a non-positive pivot was met
+};
+size_t factor_solve_smem_bytes();
+cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s);
+
+// ---- predict.cu --------------------------------------------------------------------------
+struct PredictParams {
+    const CentreTask* tasks;
+    int n_tasks;
+    int k, kp;
+    const double* work;   // as above; Zt = rows kp.. of each task's block
+    const double* XtY;    // (V x Dp)
+    int Dp;               // feature count rounded up to 64
+    double* yhat;         // per task: EVAL_PAD x Dp
+};
+size_t predict_smem_bytes();
+cudaError_t launch_predict(const PredictParams& p, cudaStream_t s);
+
+// ---- score.cu ----------------------------------------------------------------------------
+struct ScoreParams {
+    const CentreTask* tasks;
+    int n_tasks;
+    const double* yhat;        // per task EVAL_PAD x Dp; rows: captions, images, imagery, zero pad
+    int Dp;
+    const __half* cand;        // (EVAL_PAD x Dp) candidate latents, rows ordered like yhat rows
+    const double* cand_sq;     // squared norms of the candidate rows
+    int n_cap, n_img, n_im;
+    double* scores;            // (n_centres x 8), written at row task.centre
+};
+size_t score_smem_bytes(int Dp);
+cudaError_t launch_score(const ScoreParams& p, cudaStream_t s);
+
+// ---- prep.cu -----------------------------------------------------------------------------
+cudaError_t launch_prep_tasks(const int* adjacency, int k, int kp, const int* task_row, const long* task_union_off,
+                              const int* task_union_n, const int* union_vertices, int n_vertices, int n_tasks,
+                              int* nbr_sorted, int* loc, int* bad_index_flag, cudaStream_t s);
+__global__ void gather_rows_f16_kernel(const __half* Y, long ldy, const int* rows, int n_rows, int D, __half* out,
+                                       int n_out, int ld_out);
+
+// ---- knn.cu ------------------------------------------------------------------------------
+// coords: (V x 3) float64 device; queries q_begin..q_end-1 are rows of coords; outputs are indexed from q_begin.
+cudaError_t launch_knn(const double* coords, int V, int k, int q_begin, int q_end, int64_t* idx_out,
+                       double* dist_out, int* overflow_flag, cudaStream_t s);
+
+}  // namespace mmd

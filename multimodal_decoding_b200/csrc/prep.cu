@@ -1,0 +1,87 @@
+// Per-task index preparation: order a centre's neighbour list by vertex id and locate every
+// neighbour inside its cluster's (sorted) union list.  With both lists ascending, the centre's
+// k x k Gram is the sub-matrix G_U[loc, loc] and (row >= col) always lands in the stored lower triangle.
+// The ridge solution does not depend on the order of the neighbourhood columns
+// (searchlight.py:110 only fixes *which* columns enter the fit).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace mmd {
+
+__global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__ adjacency, int k, int kp,
+                                                         const int* __restrict__ task_row,
+                                                         const long* __restrict__ task_union_off,
+                                                         const int* __restrict__ task_union_n,
+                                                         const int* __restrict__ union_vertices, int n_vertices,
+                                                         int* __restrict__ nbr_sorted, int* __restrict__ loc,
+                                                         int* __restrict__ bad_index_flag) {
+    extern __shared__ int sm[];                 // next power of two >= k
+    const int t = blockIdx.x, tid = threadIdx.x;
+    int np2 = 1;
+    while (np2 < k) np2 <<= 1;
+    const int* row = adjacency + (long)task_row[t] * k;
+    for (int i = tid; i < np2; i += blockDim.x) {
+        int v = i < k ? row[i] : 0x7fffffff;
+        if (i < k && (v < 0 || v >= n_vertices)) {
+            atomicExch(bad_index_flag, 1);
+            v = 0;
+        }
+        sm[i] = v;
+    }
+    __syncthreads();
+    for (int size = 2; size <= np2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int p = tid; p < np2 / 2; p += blockDim.x) {
+                const int lo = 2 * p - (p & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const int a = sm[lo], b = sm[hi];
+                if ((a > b) == up) {
+                    sm[lo] = b;
+                    sm[hi] = a;
+                }
+            }
+            __syncthreads();
+        }
+    const int* uni = union_vertices + task_union_off[t];
+    const int un = task_union_n[t];
+    for (int i = tid; i < kp; i += blockDim.x) {
+        int v = -1, pos = -1;
+        if (i < k) {
+            v = sm[i];
+            int lo = 0, hi = un;                 // lower_bound
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (uni[mid] < v) lo = mid + 1;
+                else hi = mid;
+            }
+            pos = lo;
+            if (lo >= un || uni[lo] != v) atomicExch(bad_index_flag, 2);
+        }
+        nbr_sorted[(long)t * kp + i] = v;
+        loc[(long)t * kp + i] = pos;
+    }
+}
+
+cudaError_t launch_prep_tasks(const int* adjacency, int k, int kp, const int* task_row, const long* task_union_off,
+                              const int* task_union_n, const int* union_vertices, int n_vertices, int n_tasks,
+                              int* nbr_sorted, int* loc, int* bad_index_flag, cudaStream_t s) {
+    int np2 = 1;
+    while (np2 < k) np2 <<= 1;
+    prep_tasks_kernel<<<n_tasks, 256, np2 * sizeof(int), s>>>(adjacency, k, kp, task_row, task_union_off,
+                                                             task_union_n, union_vertices, n_vertices, nbr_sorted,
+                                                             loc, bad_index_flag);
+    return cudaGetLastError();
+}
+
+// out[j][d] = Y[rows[j]][d] for j < n_rows, d < D; zero elsewhere (out is n_out x ld_out)
+__global__ void gather_rows_f16_kernel(const __half* __restrict__ Y, long ldy, const int* __restrict__ rows,
+                                       int n_rows, int D, __half* __restrict__ out, int n_out, int ld_out) {
+    const int j = blockIdx.x;
+    for (int d = threadIdx.x; d < ld_out; d += blockDim.x) {
+        __half v = __float2half(0.f);
+        if (j < n_rows && d < D) v = Y[(long)rows[j] * ldy + d];
+        out[(long)j * ld_out + d] = v;
+    }
+}
+
+}  // namespace mmd
