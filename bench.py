@@ -1,0 +1,435 @@
+"""Benchmark of the searchlight ridge-decoding hot path (BASELINE.json metric: searchlight centres/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1]): one synthetic fsaverage7-sized hemisphere (icosphere-7, 163,842 vertices),
+k = 750 nearest neighbours, N_train = 4000, 140 test + 3 imagery trials, D = 1024 (ImageBind), alpha = 1,
+modality-agnostic.  A *step* is one call of the hot path on `--centres-per-step` consecutive centres of the rank's
+vertex shard (successive steps walk through the shard).  `value` is measured with the trial arrays already staged in
+HBM; `e2e` calls the public drop-in `custom_search_light` with HOST buffers every step (pinned X, y, adjacency rows
+in; score dicts out).  With N > 1 (torchrun) every rank works on its own contiguous vertex range ("weak" scaling,
+no data-path collective; the score blocks are all-gathered once per step).
+
+`--impl reference` times the CPU restatement of the reference's per-centre loop (oracle/, float64 numpy/scipy with
+all host threads) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "searchlight centers/sec (750-nbr ridge+pairwise acc)"
+UNIT = "centers/s"
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--mesh-level", type=int, default=7, help="icosphere level (7 = 163,842 vertices)")
+    p.add_argument("--n-neighbors", type=int, default=750)
+    p.add_argument("--n-train", type=int, default=4000)
+    p.add_argument("--n-dims", type=int, default=1024)
+    p.add_argument("--centres-per-step", type=int, default=8192)
+    p.add_argument("--cpu-centres", type=int, default=48, help="centres of the CPU-baseline sample")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-e2e", action="store_true")
+    return p.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------------------
+# synthetic workload
+# ----------------------------------------------------------------------------------------------------------
+def make_workload(args, device):
+    """Mesh on the host (numpy), trials on the GPU (torch as plumbing): low-rank stimulus signal with smooth spatial
+    loadings plus noise, z-scored with the TRAIN statistics and cast to float16 exactly like searchlight.py:199-248."""
+    import torch
+    from multimodal_decoding_b200 import synthetic as syn
+    mesh = syn.make_mesh(level=args.mesh_level, seed=7)
+    coords = mesh.coords
+    V = len(coords)
+    n_tr, n_te, n_im, D, r = args.n_train, 140, 3, args.n_dims, 32
+    g = torch.Generator(device=device).manual_seed(0)
+    z_tr = torch.randn(n_tr, r, device=device, generator=g)
+    z_half = torch.randn(70, r, device=device, generator=g)
+    z = torch.cat([z_tr, z_half, z_half, torch.randn(n_im, r, device=device, generator=g)])
+    mix = torch.randn(r, D, device=device, generator=g)
+    Y = z @ mix + 0.5 * torch.randn(len(z), D, device=device, generator=g)
+    Y[n_tr + 70:n_tr + 140] = Y[n_tr:n_tr + 70]                     # caption i and image i share a latent (`avg`)
+    c = torch.from_numpy(coords).to(device)
+    bumps = c[torch.randint(0, V, (r,), device=device, generator=g)]
+    load = torch.exp(-0.5 * torch.cdist(c, bumps) ** 2 / 20.0 ** 2)  # (V, r) smooth loadings, sigma 20 mm
+    X = torch.empty(len(z), V, device=device, dtype=torch.float32)
+    for lo in range(0, len(z), 512):                                # row blocks keep the temporaries small
+        hi = min(lo + 512, len(z))
+        X[lo:hi] = 0.35 * (z[lo:hi] @ load.T) + torch.randn(hi - lo, V, device=device, generator=g)
+
+    def zscore(a):
+        mu, sd = a[:n_tr].mean(0), a[:n_tr].std(0, unbiased=False)
+        sd[sd == 0] = 1
+        return ((a - mu) / sd).to(torch.float16)
+
+    X16, Y16 = zscore(X), zscore(Y)
+    del X
+    ids = (list(range(n_tr)), list(range(n_tr, n_tr + n_te)), list(range(n_tr + n_te, n_tr + n_te + n_im)))
+    return coords, X16, Y16, ids
+
+
+# ----------------------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe)
+# ----------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle's restatement of the reference loop (float64, BLAS on all host threads)
+# ----------------------------------------------------------------------------------------------------------
+def cpu_centres_per_sec(X, Y, A_rows, ids, n_centres, budget_s=30.0):
+    from oracle import searchlight_oracle as orc          # bench.py's cpu_baseline leg may run the oracle
+    tr, te, im = ids
+    is_cap = orc.default_is_caption(len(te))
+    orc.search_light(X, Y, A_rows, tr, te, im, 1.0, is_cap, centres=[0])          # warm the BLAS threads
+    t0, done = time.perf_counter(), 0
+    for c in range(min(n_centres, len(A_rows))):
+        orc.search_light(X, Y, A_rows, tr, te, im, 1.0, is_cap, centres=[c])
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return done / dt, done, dt
+
+
+def host_threads():
+    try:
+        from threadpoolctl import threadpool_info
+        n = [p["num_threads"] for p in threadpool_info() if p.get("user_api") == "blas"]
+        if n:
+            return max(n)
+    except Exception:
+        pass
+    return os.cpu_count() or 1
+
+
+# ----------------------------------------------------------------------------------------------------------
+# roofline bookkeeping
+# ----------------------------------------------------------------------------------------------------------
+FP64_TENSOR_PEAK_TFLOPS = 37.1      # DMMA m8n8k4, measured on this pool with tools/peak_probe.cu (gpurun_out_peaks.log)
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"], "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "source": "fallback"}
+
+
+def stage_flops_per_centre(stage, k, n_train, n_eval_pad, D):
+    """EXECUTED float64 flops per centre of each per-centre kernel.  The Gram stage is
+    accounted from the library's own executed-flop counter because it depends on the cluster unions."""
+    kp = (k + 63) // 64 * 64
+    ldt = (n_train + 63) // 64 * 64
+    Dp = (D + 63) // 64 * 64
+    return {
+        "factor_solve": kp ** 3 / 3.0 + 2.0 * kp * kp * n_eval_pad,     # Cholesky + forward and backward solves, 144 RHS
+        "predict": 2.0 * n_eval_pad * kp * Dp,
+        "syrk_algorithmic": 2.0 * n_train * k * k,                      # what the reference executes per centre
+        "ldt": ldt,
+    }[stage]
+
+
+def roofline_entry(stats, n_centres, args, peaks):
+    ms = stats["stage_ms"]
+    per_centre = ["prep", "syrk", "factor_solve", "predict", "score"]
+    top = max(per_centre, key=lambda s: ms[s])
+    k, ntr, D = args.n_neighbors, args.n_train, args.n_dims
+    t = ms[top] * 1e-3
+    shares = {s: round(ms[s] / max(sum(ms[x] for x in per_centre), 1e-9), 4) for s in per_centre}
+    out = {"kernel": top, "stage_ms": {s: round(ms[s], 3) for s in per_centre}, "stage_share": shares}
+    if top in ("syrk", "factor_solve", "predict"):
+        executed = stats["syrk_flops"] if top == "syrk" else stage_flops_per_centre(top, k, ntr, 144, D) * n_centres
+        achieved = executed / t / 1e12
+        out.update({"bound": "tensor", "achieved": round(achieved, 3), "peak": FP64_TENSOR_PEAK_TFLOPS,
+                    "unit": "TFLOP/s", "frac": round(achieved / FP64_TENSOR_PEAK_TFLOPS, 4), "traffic": None,
+                    "peak_source": "fp64 tensor pipe (DMMA) measured with tools/peak_probe.cu on this pool; "
+                                   "MEASURED_PEAKS.json holds no fp64 figure",
+                    "frac_of_bf16_peak": round(achieved / peaks["bf16_tflops"], 5),
+                    "flops": "executed float64 flops (<= the reference's algorithmic count)"})
+        if top == "syrk":
+            out["algorithmic_equiv_tflops"] = round(2.0 * ntr * k * k * n_centres / t / 1e12, 2)
+    else:
+        n_eval = 143
+        bytes_alg = n_centres * (144.0 * ((D + 63) // 64 * 64) * 8 + 64) if top == "score" else n_centres * k * 8.0
+        achieved = bytes_alg / t / 1e9
+        out.update({"bound": "hbm", "achieved": round(achieved, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                    "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": None,
+                    "peak_source": peaks["source"]})
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------------
+# arms
+# ----------------------------------------------------------------------------------------------------------
+def dist_setup(args):
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def knn_rows(eng, coords, k, lo, hi, chunk=32768):
+    """Adjacency rows lo..hi (the k-NN branch of get_adjacency_matrix) from the GPU kernel, as int64 like sklearn."""
+    out = np.empty((hi - lo, k), dtype=np.int64)
+    for s in range(lo, hi, chunk):
+        e = min(s + chunk, hi)
+        _, idx = eng.knn(coords, k, s, e)
+        out[s - lo:e - lo] = idx
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+    from multimodal_decoding_b200.sharding import split_bounds
+    from sklearn.linear_model import Ridge
+
+    rank, world, local = dist_setup(args)
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    eng = sl.get_engine(local)
+    stream = torch.cuda.ExternalStream(eng.stream_ptr, device=device)
+    K, W, cps, k = args.steps, args.warmup, args.centres_per_step, args.n_neighbors
+
+    t_setup = time.perf_counter()
+    coords, X16, Y16, ids = make_workload(args, device)
+    V = len(coords)
+    lo, hi = split_bounds(V, world)[rank]
+    cps = min(cps, hi - lo)
+    n_rows = min(hi - lo, (W + K) * cps)
+    torch.cuda.synchronize()
+    t_knn = time.perf_counter()
+    A = knn_rows(eng, coords, k, lo, lo + n_rows)
+    knn_s = time.perf_counter() - t_knn
+    is_cap = np.arange(140) < 70
+    estimator = Ridge(alpha=1.0, fit_intercept=False)
+
+    def rows_of(step):
+        s = (step * cps) % max(n_rows - cps + 1, 1)
+        return A[s:s + cps]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident arm: X / y staged once, adjacency rows in, score block out -------------------------
+    t_up = time.perf_counter()
+    eng.upload(X16, Y16, ids[0], ids[1], ids[2], is_cap)
+    upload_s = time.perf_counter() - t_up
+    upload_stats = eng.stats()
+    setup_s = time.perf_counter() - t_setup
+    for s in range(W):
+        eng.searchlight(rows_of(s), 1.0)
+    eng.reset_stats()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with ClockSampler(local) as clocks:
+        ev0.record(stream)
+        t0 = time.perf_counter()
+        for s in range(W, W + K):
+            scores, flags = eng.searchlight(rows_of(s), 1.0)
+            if world > 1:
+                from multimodal_decoding_b200.sharding import gather_scores
+                gather_scores(scores, cps * world)           # the path's one collective: (V_shard x 8) blocks
+        ev1.record(stream)
+        barrier()
+        wall = time.perf_counter() - t0
+    dev_s = max_over_ranks(ev0.elapsed_time(ev1) * 1e-3)
+    wall = max_over_ranks(wall)
+    stats = eng.stats()
+    value = world * cps * K / dev_s
+
+    # ---- end to end through the public drop-in, host buffers every step -----------------------------------
+    e2e = None
+    if not args.no_e2e:
+        Xh = torch.empty(X16.shape, dtype=torch.float16, pin_memory=True).copy_(X16).numpy()
+        Yh = torch.empty(Y16.shape, dtype=torch.float16, pin_memory=True).copy_(Y16).numpy()
+        del X16, Y16
+
+        def e2e_step(step):
+            rows = rows_of(step)
+            if world > 1:                       # custom_search_light takes the r-th contiguous range itself
+                full = np.zeros((world * cps, k), dtype=np.int64)
+                full[rank * cps:(rank + 1) * cps] = rows
+                rows = full
+            return sl.custom_search_light(Xh, Yh, estimator, rows, ids[0], ids[1], ids[2], n_jobs=world)
+
+        for s in range(min(W, 3)):
+            e2e_step(s)
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(W, W + K):
+            out = e2e_step(s)
+        barrier()
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        assert len(out) == world * cps and len(out[0]) == 8
+        h2d = Xh.nbytes + Yh.nbytes + cps * k * 4
+        e2e = {"value": round(world * cps * K / e2e_s, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(cps * (8 * 8 + 4)), "ms_per_step": round(e2e_s / K * 1e3, 2),
+               "api": "custom_search_light(X_host_f16, y_host_f16, Ridge(alpha=1), A_rows, ...)"}
+    else:
+        Xh, Yh = X16.cpu().numpy(), Y16.cpu().numpy()
+
+    cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        v, n, dt = cpu_centres_per_sec(Xh, Yh, A[:args.cpu_centres], ids, args.cpu_centres)
+        cpu = {"value": round(v, 3), "unit": UNIT, "cores": host_threads(), "kind": "port",
+               "sample": f"{n} consecutive centres of the same workload in {dt:.1f} s (float64 numpy/scipy oracle, "
+                         f"one centre at a time, BLAS threads = cores)"}
+    if rank == 0:
+        peaks = load_peaks()
+        line = {
+            "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(dev_s / K * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "searchlight imagebind --n-neighbors 750 modality-agnostic, one synthetic "
+                                   "fsaverage7-sized hemisphere (BASELINE.json configs[1])",
+                       "n_vertices": V, "n_neighbors": k, "n_train": args.n_train, "n_test": 140, "n_imagery": 3,
+                       "n_dims": args.n_dims, "alpha": 1.0, "centres_per_step_per_gpu": cps,
+                       "sharding": f"vertex ranges x{world}", "l2": "inputs larger than L2 (Xt 1.3 GB, per-step "
+                       "workspaces > 126 MB); no flush needed"},
+            "wall_ms_per_step": round(wall / K * 1e3, 3),
+            "e2e": e2e, "gpu_launches": int(stats["launches"]),
+            "roofline": roofline_entry(stats, cps * K, args, peaks),
+            "cpu_baseline": cpu, "clocks": clocks.summary(),
+            "setup": {"knn_rows": int(n_rows), "knn_s": round(knn_s, 2), "upload_s": round(upload_s, 3),
+                      "upload_stage_ms": {s: round(v, 2) for s, v in upload_stats["stage_ms"].items() if v > 0},
+                      "total_s": round(setup_s, 1)},
+            "clusters_per_step": stats["clusters"] / K,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """The reference's CPU path for the same workload: per-centre float64 ridge + scoring on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from multimodal_decoding_b200 import synthetic as syn
+    from oracle import searchlight_oracle as orc
+    k, n_tr, D = args.n_neighbors, args.n_train, args.n_dims
+    n_c = 4                                                     # centres per step (bounded sample)
+    mesh = syn.make_mesh(level=args.mesh_level, seed=7)
+    rng = np.random.default_rng(0)
+    # the neighbourhood columns of the sampled centres only: same shapes/dtypes as the GPU arm's workload
+    c64 = mesh.coords.astype(np.float64)
+    centres = np.arange((args.warmup + args.steps) * n_c)
+    nbrs = []
+    for c in centres:
+        d = c64 - c64[c]
+        nbrs.append(np.argsort((d[:, 0] ** 2 + d[:, 1] ** 2) + d[:, 2] ** 2, kind="stable")[:k])
+    used = np.unique(np.concatenate(nbrs))
+    remap = {v: i for i, v in enumerate(used)}
+    A = np.array([[remap[v] for v in nb] for nb in nbrs])
+    n_total = n_tr + 143
+    z = rng.standard_normal((n_total, 32))
+    X = (0.35 * z @ rng.standard_normal((32, len(used))) + rng.standard_normal((n_total, len(used))))
+    Y = z @ rng.standard_normal((32, D)) + 0.5 * rng.standard_normal((n_total, D))
+    X = ((X - X[:n_tr].mean(0)) / X[:n_tr].std(0)).astype(np.float16)
+    Y = ((Y - Y[:n_tr].mean(0)) / Y[:n_tr].std(0)).astype(np.float16)
+    ids = (np.arange(n_tr), np.arange(n_tr, n_tr + 140), np.arange(n_tr + 140, n_total))
+    is_cap = orc.default_is_caption(140)
+    step = lambda s: orc.search_light(X, Y, A, *ids, 1.0, is_cap, centres=list(range(s * n_c, (s + 1) * n_c)))
+    for s in range(args.warmup):
+        step(s)
+    t0 = time.perf_counter()
+    for s in range(args.warmup, args.warmup + args.steps):
+        step(s)
+    dt = time.perf_counter() - t0
+    v = n_c * args.steps / dt
+    sample = f"{n_c} centres per step x {args.steps} steps, k={k}, N_train={n_tr}, D={D}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "searchlight imagebind --n-neighbors 750 modality-agnostic (BASELINE.json configs[1]), "
+                               "bounded sample of centres", "n_neighbors": k, "n_train": n_tr, "n_dims": D},
+        "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": host_threads(), "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "CPU restatement of the reference loop (the reference is Python + sklearn/scipy and cannot travel "
+                "to the GPU box); float64, BLAS on all host threads"}), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    run_reference(a) if a.impl == "reference" else run_ours(a)

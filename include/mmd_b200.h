@@ -38,6 +38,10 @@ void mmd_destroy(mmd_handle* h);
 const char* mmd_last_error(const mmd_handle* h);
 const char* mmd_version(void);
 
+/* The CUDA stream (cudaStream_t) every kernel of this handle is launched on, so that a caller can bracket calls
+ * with its own CUDA events (bench.py does; the reference only has wall-clock timing, searchlight.py:250-257). */
+void* mmd_stream(mmd_handle* h);
+
 /* Name of score column i (0..7), e.g. "pairwise_acc_captions"; eval.py:9-44 and searchlight.py:87. */
 const char* mmd_score_name(int i);
 

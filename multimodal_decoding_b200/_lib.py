@@ -11,7 +11,7 @@ EVAL_PAD = 144
 
 EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_upload",
-    "mmd_searchlight", "mmd_predict_centre", "mmd_get_stats", "mmd_reset_stats", "mmd_stage_name", "mmd_configure",
+    "mmd_searchlight", "mmd_predict_centre", "mmd_get_stats", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
 ]
 
 _lib = None
@@ -35,6 +35,8 @@ def load():
     lib.mmd_last_error.argtypes = [vp]
     lib.mmd_last_error.restype = C.c_char_p
     lib.mmd_version.restype = C.c_char_p
+    lib.mmd_stream.argtypes = [vp]
+    lib.mmd_stream.restype = vp
     lib.mmd_score_name.argtypes = [i32]
     lib.mmd_score_name.restype = C.c_char_p
     lib.mmd_stage_name.argtypes = [i32]

@@ -446,6 +446,8 @@ void mmd_destroy(mmd_handle* h) {
     delete h;
 }
 
+void* mmd_stream(mmd_handle* h) { return h ? (void*)h->stream : nullptr; }
+
 const char* mmd_last_error(const mmd_handle* h) { return h ? h->err.c_str() : "null handle"; }
 
 int mmd_configure(mmd_handle* h, int cluster_size, int batch_centres, int host_threads) {

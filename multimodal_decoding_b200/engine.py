@@ -123,6 +123,11 @@ class Engine:
         self._check(self._lib.mmd_predict_centre(self._h, nb.ctypes.data, len(nb), float(alpha), out.ctypes.data))
         return out
 
+    @property
+    def stream_ptr(self) -> int:
+        """cudaStream_t of the handle (wrap with torch.cuda.ExternalStream to record events on it)."""
+        return int(self._lib.mmd_stream(self._h) or 0)
+
     # -- statistics --------------------------------------------------------------------------
     def reset_stats(self):
         self._lib.mmd_reset_stats(self._h)

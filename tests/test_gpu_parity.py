@@ -1,0 +1,160 @@
+"""Parity of the CUDA path (through the C ABI, libmmd_b200.so) against the golden fixtures written by the
+unmodified reference and against the float64 oracle.  Needs a B200: run with `-m gpu`."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import searchlight_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-3          # BASELINE.json north_star: per-vertex accuracies within 1e-3 absolute
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from multimodal_decoding_b200.engine import Engine
+    eng = Engine(0)
+    yield eng
+    eng.close()
+
+
+def _ids(g):
+    ntr, nte, nim = int(g["n_train"]), int(g["n_test"]), int(g["n_imagery"])
+    return np.arange(ntr), np.arange(ntr, ntr + nte), np.arange(ntr + nte, ntr + nte + nim)
+
+
+def test_knn_bit_exact(engine, golden_dir):
+    g = np.load(os.path.join(golden_dir, "knn_small.npz"))
+    for c, a, d in (("coords", "adjacency", "distances"), ("coords2", "adjacency2", "distances2")):
+        dist, idx = engine.knn(g[c], g[a].shape[1])
+        assert idx.dtype == np.int64
+        assert np.array_equal(idx, g[a].astype(np.int64))
+        assert np.array_equal(dist, g[d])
+    # a query sub-range gives the same rows
+    dist, idx = engine.knn(g["coords"], 48, 100, 164)
+    assert np.array_equal(idx, g["adjacency"][100:164].astype(np.int64))
+
+
+@pytest.mark.parametrize("name", ["searchlight_small.npz", "searchlight_smooth.npz", "searchlight_captions.npz"])
+def test_searchlight_matches_reference_fixture(engine, golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name))
+    tr, te, im = _ids(g)
+    engine.upload(g["X"], g["latents"], tr, te, im, orc.default_is_caption(len(te)))
+    scores, flags = engine.searchlight(g["adjacency"], float(g["alpha"]))
+    assert flags.sum() == 0
+    want = g["scores"]
+    assert np.abs(scores - want).max() <= TOL
+    # scores are counts / constants: the float64 pipeline reproduces the reference's counts exactly
+    assert np.array_equal(scores, want)
+
+
+def test_predictions_match_oracle(engine, golden_dir):
+    g = np.load(os.path.join(golden_dir, "searchlight_smooth.npz"))
+    tr, te, im = _ids(g)
+    is_cap = orc.default_is_caption(len(te))
+    engine.upload(g["X"], g["latents"], tr, te, im, is_cap)
+    for c in (0, 17, len(g["adjacency"]) - 1):
+        nb = g["adjacency"][c]
+        yh = engine.predict_centre(nb, 1.0)
+        _, pt, pi = orc.train_and_test(g["X"][:, nb], g["latents"], tr, te, im, 1.0, is_cap, return_preds=True)
+        ref = np.concatenate([pt[is_cap], pt[~is_cap], pi])
+        assert np.abs(yh - ref).max() <= 1e-9 * np.abs(ref).max()
+
+
+def test_device_pointers_and_subsets(engine, golden_dir):
+    """X / y may already live on the GPU (borrowed torch tensors); a subset of centres in any order gives the
+    same rows (centres are independent)."""
+    import torch
+    g = np.load(os.path.join(golden_dir, "searchlight_small.npz"))
+    tr, te, im = _ids(g)
+    Xd = torch.from_numpy(g["X"]).cuda()
+    Yd = torch.from_numpy(g["latents"]).cuda()
+    engine.upload(Xd, Yd, tr, te, im, orc.default_is_caption(len(te)))
+    rng = np.random.default_rng(0)
+    pick = rng.permutation(len(g["adjacency"]))[:97]
+    scores, _ = engine.searchlight(g["adjacency"][pick], float(g["alpha"]))
+    assert np.array_equal(scores, g["scores"][pick])
+
+
+def test_non_contiguous_trial_ids_and_stim_order(engine):
+    """Arbitrary id lists (searchlight.py:50-55 index with lists) and an interleaved caption mask."""
+    from multimodal_decoding_b200 import synthetic as syn
+    mesh = syn.make_mesh(level=None, n_points=400, seed=3)
+    trials = syn.make_trials(mesh, n_train=200, n_dims=40, n_factors=6, iid=True, seed=5, n_test_per_mod=20)
+    inp = syn.make_searchlight_inputs(mesh, trials)
+    rng = np.random.default_rng(1)
+    perm = rng.permutation(len(inp.X))
+    X, Y = inp.X[perm], inp.latents[perm]
+    inv = np.argsort(perm)
+    tr, te, im = inv[inp.train_ids], inv[inp.test_ids], inv[inp.imagery_ids]
+    is_cap = np.zeros(len(te), dtype=bool)
+    is_cap[::2] = True
+    _, A = orc.knn_adjacency(inp.coords, 24)
+    want = orc.search_light(X, Y, A, tr, te, im, alpha=2.5, is_caption=is_cap)
+    engine.upload(X, Y, tr, te, im, is_cap)
+    got, flags = engine.searchlight(A, 2.5)
+    assert flags.sum() == 0
+    assert np.array_equal(got, want)
+
+
+def test_medium_k750_against_oracle(engine):
+    """Full-size neighbourhoods (k=750, N_train=4000, D=1024) on a 10k-vertex mesh: a sample of centres is
+    checked against the oracle; margins show the comparisons are not at rounding level."""
+    from multimodal_decoding_b200 import synthetic as syn
+    mesh = syn.make_mesh(level=5, seed=7)                      # 10,242 vertices
+    trials = syn.make_trials(mesh, n_train=4000, n_dims=1024, seed=0)
+    inp = syn.make_searchlight_inputs(mesh, trials)
+    dist, A = engine.knn(inp.coords, 750)
+    centres = np.arange(0, len(A), 41)[:256]
+    is_cap = orc.default_is_caption(140)
+    engine.upload(inp.X, inp.latents, inp.train_ids, inp.test_ids, inp.imagery_ids, is_cap)
+    got, flags = engine.searchlight(A[centres], 1.0)
+    assert flags.sum() == 0
+    sample = centres[::16]
+    want = orc.search_light(inp.X, inp.latents, A, inp.train_ids, inp.test_ids, inp.imagery_ids, alpha=1.0,
+                            centres=list(sample))
+    assert np.abs(got[::16] - want).max() <= TOL
+    assert np.array_equal(got[::16], want)
+    # neighbour lists: oracle brute force on the sampled rows
+    c64 = inp.coords.astype(np.float64)
+    for c in sample[:4]:
+        d = c64 - c64[c]
+        d2 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+        assert np.array_equal(np.argsort(d2, kind="stable")[:750], A[c])
+
+
+def test_properties_full_width(engine):
+    """Size-independent properties: centre order invariance, neighbour order invariance, alpha monotone effect."""
+    from multimodal_decoding_b200 import synthetic as syn
+    mesh = syn.make_mesh(level=4, seed=9)
+    trials = syn.make_trials(mesh, n_train=600, n_dims=128, seed=2)
+    inp = syn.make_searchlight_inputs(mesh, trials)
+    _, A = engine.knn(inp.coords, 200)
+    engine.upload(inp.X, inp.latents, inp.train_ids, inp.test_ids, inp.imagery_ids, orc.default_is_caption(140))
+    base, _ = engine.searchlight(A, 1.0)
+    assert np.all((base >= 0) & (base <= 1))
+    rev, _ = engine.searchlight(A[::-1], 1.0)
+    assert np.array_equal(rev[::-1], base)
+    rng = np.random.default_rng(0)
+    Ash = np.stack([rng.permutation(r) for r in A[:300]])
+    sh, _ = engine.searchlight(Ash, 1.0)
+    # permuting the neighbours permutes rows/columns of the normal equations: same predictions up to rounding
+    assert np.abs(sh - base[:300]).max() <= TOL
+
+
+def test_errors(engine, golden_dir):
+    g = np.load(os.path.join(golden_dir, "searchlight_small.npz"))
+    tr, te, im = _ids(g)
+    engine.upload(g["X"], g["latents"], tr, te, im, orc.default_is_caption(len(te)))
+    bad = g["adjacency"][:4].copy()
+    bad[2, 5] = g["X"].shape[1] + 3
+    with pytest.raises(RuntimeError, match="outside"):
+        engine.searchlight(bad, 1.0)
+    with pytest.raises(RuntimeError, match="exceeds n_train"):
+        engine.searchlight(np.tile(np.arange(len(tr) + 8, dtype=np.int32) % g["X"].shape[1], (2, 1)), 1.0)
+    with pytest.raises(TypeError):
+        engine.upload(g["X"].astype(np.float32), g["latents"], tr, te, im, orc.default_is_caption(len(te)))
+    scores, _ = engine.searchlight(g["adjacency"][:0], 1.0)
+    assert scores.shape == (0, 8)
