@@ -643,8 +643,8 @@ int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int 
         CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
-    if (bad == 1) return fail(h, "mmd_searchlight: adjacency holds a vertex index outside [0, %d)", h->V);
-    if (bad == 2) return fail(h, "internal: neighbour missing from its cluster union");
+    if (bad == 2) return fail(h, "mmd_searchlight: adjacency holds a vertex index outside [0, %d)", h->V);
+    if (bad == 1) return fail(h, "internal: neighbour missing from its cluster union");
     return 0;
 }
 

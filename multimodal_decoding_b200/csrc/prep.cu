@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
     for (int i = tid; i < np2; i += blockDim.x) {
         int v = i < k ? row[i] : 0x7fffffff;
         if (i < k && (v < 0 || v >= n_vertices)) {
-            atomicExch(bad_index_flag, 1);
+            atomicMax(bad_index_flag, 2);       // 2 = vertex id out of range (wins over 1)
             v = 0;
         }
         sm[i] = v;
@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
                 else hi = mid;
             }
             pos = lo;
-            if (lo >= un || uni[lo] != v) atomicExch(bad_index_flag, 2);
+            if (lo >= un || uni[lo] != v) atomicMax(bad_index_flag, 1);   // 1 = not in the union
         }
         nbr_sorted[(long)t * kp + i] = v;
         loc[(long)t * kp + i] = pos;
