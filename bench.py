@@ -35,14 +35,18 @@ UNIT = "centers/s"
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--steps", type=int, default=3)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--mesh-level", type=int, default=7, help="icosphere level (7 = 163,842 vertices)")
     p.add_argument("--n-neighbors", type=int, default=750)
     p.add_argument("--n-train", type=int, default=4000)
     p.add_argument("--n-dims", type=int, default=1024)
-    p.add_argument("--centres-per-step", type=int, default=8192)
+    p.add_argument("--centres-per-step", type=int, default=0,
+                   help="centres per step and GPU; 0 = the whole hemisphere (weak) or the rank's whole shard (strong)")
+    p.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                   help="weak: every GPU runs one whole hemisphere job per step (configs[4] distributes whole "
+                        "searchlights); strong: ONE hemisphere, centres sharded across the GPUs")
     p.add_argument("--cpu-centres", type=int, default=48, help="centres of the CPU-baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
@@ -52,7 +56,7 @@ def parse_args():
 # ----------------------------------------------------------------------------------------------------------
 # synthetic workload
 # ----------------------------------------------------------------------------------------------------------
-def make_workload(args, device):
+def make_workload(args, device, seed=0):
     """Mesh on the host (numpy), trials on the GPU (torch as plumbing): low-rank stimulus signal with smooth spatial
     loadings plus noise, z-scored with the TRAIN statistics and cast to float16 exactly like searchlight.py:199-248."""
     import torch
@@ -61,7 +65,7 @@ def make_workload(args, device):
     coords = mesh.coords
     V = len(coords)
     n_tr, n_te, n_im, D, r = args.n_train, 140, 3, args.n_dims, 32
-    g = torch.Generator(device=device).manual_seed(0)
+    g = torch.Generator(device=device).manual_seed(seed)
     z_tr = torch.randn(n_tr, r, device=device, generator=g)
     z_half = torch.randn(70, r, device=device, generator=g)
     z = torch.cat([z_tr, z_half, z_half, torch.randn(n_im, r, device=device, generator=g)])
@@ -249,7 +253,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
-    from multimodal_decoding_b200.sharding import split_bounds
+    from multimodal_decoding_b200.sharding import spatial_order, split_bounds
     from sklearn.linear_model import Ridge
 
     rank, world, local = dist_setup(args)
@@ -260,15 +264,22 @@ def run_ours(args):
     K, W, cps, k = args.steps, args.warmup, args.centres_per_step, args.n_neighbors
 
     t_setup = time.perf_counter()
-    coords, X16, Y16, ids = make_workload(args, device)
+    weak = args.scaling == "weak" or world == 1
+    coords, X16, Y16, ids = make_workload(args, device, seed=rank if weak else 0)
     V = len(coords)
-    lo, hi = split_bounds(V, world)[rank]
-    cps = min(cps, hi - lo)
-    n_rows = min(hi - lo, (W + K) * cps)
     torch.cuda.synchronize()
     t_knn = time.perf_counter()
-    A = knn_rows(eng, coords, k, lo, lo + n_rows)
+    A_all = knn_rows(eng, coords, k, 0, V)                      # k-NN branch of get_adjacency_matrix, all vertices
     knn_s = time.perf_counter() - t_knn
+    # weak: this rank's job is one whole hemisphere (its own subject/hemisphere, seed = rank), in the
+    # reference's vertex order.  strong: one hemisphere; the rows are put in Morton order first so that the
+    # contiguous range a rank receives (the reference's array_split chunking) is a compact patch of cortex.
+    order = np.arange(V) if weak and args.centres_per_step == 0 else spatial_order(coords)
+    A_all = A_all[order]
+    lo, hi = (0, V) if weak else split_bounds(V, world)[rank]
+    cps = hi - lo if args.centres_per_step == 0 else min(args.centres_per_step, hi - lo)
+    n_rows = min(hi - lo, (W + K) * cps)
+    A = A_all[lo:lo + n_rows]
     is_cap = np.arange(140) < 70
     estimator = Ridge(alpha=1.0, fit_intercept=False)
 
@@ -324,11 +335,11 @@ def run_ours(args):
 
         def e2e_step(step):
             rows = rows_of(step)
-            if world > 1:                       # custom_search_light takes the r-th contiguous range itself
-                full = np.zeros((world * cps, k), dtype=np.int64)
-                full[rank * cps:(rank + 1) * cps] = rows
-                rows = full
-            return sl.custom_search_light(Xh, Yh, estimator, rows, ids[0], ids[1], ids[2], n_jobs=world)
+            if weak:                            # n_jobs=1: the whole job on this process's GPU, no collective
+                return sl.custom_search_light(Xh, Yh, estimator, rows, ids[0], ids[1], ids[2], n_jobs=1)
+            full = np.zeros((world * cps, k), dtype=np.int64)   # custom_search_light takes the r-th range itself
+            full[rank * cps:(rank + 1) * cps] = rows
+            return sl.custom_search_light(Xh, Yh, estimator, full, ids[0], ids[1], ids[2], n_jobs=world)
 
         for s in range(min(W, 3)):
             e2e_step(s)
@@ -338,7 +349,7 @@ def run_ours(args):
             out = e2e_step(s)
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
-        assert len(out) == world * cps and len(out[0]) == 8
+        assert len(out) == (cps if weak else world * cps) and len(out[0]) == 8
         h2d = Xh.nbytes + Yh.nbytes + cps * k * 4
         e2e = {"value": round(world * cps * K / e2e_s, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(cps * (8 * 8 + 4)), "ms_per_step": round(e2e_s / K * 1e3, 2),
@@ -356,13 +367,14 @@ def run_ours(args):
         peaks = load_peaks()
         line = {
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": round(dev_s / K * 1e3, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "ms_per_step": round(dev_s / K * 1e3, 3), "higher_is_better": True,
+            "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "searchlight imagebind --n-neighbors 750 modality-agnostic, one synthetic "
                                    "fsaverage7-sized hemisphere (BASELINE.json configs[1])",
                        "n_vertices": V, "n_neighbors": k, "n_train": args.n_train, "n_test": 140, "n_imagery": 3,
                        "n_dims": args.n_dims, "alpha": 1.0, "centres_per_step_per_gpu": cps,
-                       "sharding": f"vertex ranges x{world}", "l2": "inputs larger than L2 (Xt 1.3 GB, per-step "
+                       "sharding": (f"{world} hemisphere job(s), one per GPU, score maps all-gathered" if weak else
+                                    f"one hemisphere, Morton-ordered vertex ranges x{world}, score maps all-gathered"), "l2": "inputs larger than L2 (Xt 1.3 GB, per-step "
                        "workspaces > 126 MB); no flush needed"},
             "wall_ms_per_step": round(wall / K * 1e3, 3),
             "e2e": e2e, "gpu_launches": int(stats["launches"]),

@@ -123,11 +123,13 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
 
     Under `torch.distributed` (one process per GPU) rank r scores the r-th contiguous range of
     `np.array_split(arange(V), world_size)` — the reference's own chunking — and the score blocks are gathered
-    with one all-gather; every rank returns the full array.
+    with one all-gather; every rank returns the full array.  `n_jobs=1` keeps the whole call on this process's
+    GPU even inside a process group (one whole searchlight per GPU, SURVEY.md §8e / BASELINE.json configs[4]).
     """
     from ....sharding import gather_scores, shard_range
     A = _rectangular(A)
-    lo, hi = shard_range(len(A))
+    local_only = n_jobs == 1
+    lo, hi = (0, len(A)) if local_only else shard_range(len(A))
     if null_distr_dir is not None:
         from .null_distribution import write_null_distribution
         write_null_distribution(A[lo:hi], np.arange(lo, hi), estimator, X, y, train_ids, test_ids, imagery_ids,
@@ -136,4 +138,4 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
     if verbose:
         print(f"searchlight: centres {lo}..{hi} done on device {get_engine().device}, "
               f"{int(flags.sum())} not positive definite")
-    return _scores_to_dicts(gather_scores(scores, len(A)))
+    return _scores_to_dicts(scores if local_only else gather_scores(scores, len(A)))

@@ -198,43 +198,120 @@ __device__ __forceinline__ void strip_store(const Acc& acc, double* dst, long ld
                 make_double2(acc[i][nb][0], acc[i][nb][1]);
 }
 
-// Cholesky factor of the 64x64 block in D (lower triangle used; overwritten by L_jj) and its inverse in I
-// (full block, zeros above the diagonal).  All threads of the CTA take part.
+__device__ __forceinline__ void strip_load(Acc& acc, const double* src, long ld, int lane) {
+    const int fr = lane >> 2, fk = lane & 3;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb) {
+            const double2 v = *reinterpret_cast<const double2*>(src + (long)(8 * i + fr) * ld + nb * 8 + 2 * fk);
+            acc[i][nb][0] = v.x;
+            acc[i][nb][1] = v.y;
+        }
+}
+
+// Cholesky factor of the 64x64 block in D (overwritten by L_jj, lower block triangle) and its inverse in I
+// (lower block triangle; the 8x8 diagonal blocks are written in full, zeros above the diagonal).  All threads
+// of the CTA take part.  The block is processed as an 8x8 grid of 8x8 tiles, right-looking:
+//   (A) warp 0 factors and inverts the diagonal tile in registers (one row per lane, shuffles only),
+//   (B) the tiles below it are multiplied by that inverse, (C) the trailing tiles get their rank-8 update,
+// (B) and (C) on the DMMA pipe with fragments read straight from shared memory; (D) builds the inverse of
+// the whole block by block forward substitution, one block column per warp.
 __device__ __forceinline__ void factor_invert_block(double* D, double* I, int* bad_pivot, int tid, int lane, int warp) {
-    for (int c = 0; c < NB; ++c) {
-        double d = D[c * LDD + c];
-        if (!(d > 0.0)) {
-            if (tid == 0) *bad_pivot = 1;
-            d = 1.0;
-        }
-        const double piv = sqrt(d), inv = 1.0 / piv;
-        __syncthreads();
-        if (tid < NB) {
-            if (tid > c) D[tid * LDD + c] *= inv;
-            else if (tid == c) D[c * LDD + c] = piv;
-        }
-        __syncthreads();
-        for (int r = c + 1 + warp; r < NB; r += NWARPS) {
-            const double lrc = D[r * LDD + c];
-            for (int cc = c + 1 + lane; cc <= r; cc += 32) D[r * LDD + cc] -= lrc * D[cc * LDD + c];
-        }
-        __syncthreads();
-    }
-    // inverse of the lower-triangular block: column c by forward substitution, 4 threads per column
-    if (tid < 4 * NB) {
-        const int c = tid >> 2, q = tid & 3;
-        for (int r = 0; r < NB; ++r) {
-            double s = 0.0;
-            for (int m = q; m < r; m += 4) s += D[r * LDD + m] * I[m * LDD + c];
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            if (q == 0) {
-                double x;
-                if (r < c) x = 0.0;
-                else if (r == c) x = 1.0 / D[r * LDD + r];
-                else x = -s / D[r * LDD + r];
-                I[r * LDD + c] = x;
+    const int fr = lane >> 2, fk = lane & 3;
+    for (int kk = 0; kk < 8; ++kk) {
+        if (warp == 0) {
+            // ---- (A) diagonal tile: lane r < 8 owns row r ----
+            __syncwarp();
+            double a[8], invd[8];
+            const int r = lane & 7;
+            const double* src = D + (8 * kk + r) * LDD + 8 * kk;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) a[c] = src[c];
+            bool bad = false;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                double dcc = __shfl_sync(0xffffffffu, a[c], c);
+                if (!(dcc > 0.0)) {
+                    bad = true;
+                    dcc = 1.0;
+                }
+                const double inv = rsqrt(dcc);
+                invd[c] = inv;
+                const double l = (r == c) ? dcc * inv : a[c] * inv;
+                a[c] = l;
+#pragma unroll
+                for (int cc = c + 1; cc < 8; ++cc) {
+                    const double lcc = __shfl_sync(0xffffffffu, l, cc);
+                    a[cc] = fma(-l, lcc, a[cc]);
+                }
             }
+            if (bad && lane == 0) *bad_pivot = 1;
+            // inverse, column `r` per lane: x[q] = -(sum_{m<q} L[q][m] x[m]) / L[q][q], x[m] = 0 for m < r
+            double x[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                double sum = 0.0;
+#pragma unroll
+                for (int m = 0; m < q; ++m) sum = fma(__shfl_sync(0xffffffffu, a[m], q), x[m], sum);
+                x[q] = (q == r) ? invd[q] : (q > r ? -sum * invd[q] : 0.0);
+            }
+            if (lane < 8) {
+                double* dl = D + (8 * kk + r) * LDD + 8 * kk;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) dl[c] = c <= r ? a[c] : 0.0;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) I[(8 * kk + q) * LDD + 8 * kk + r] = x[q];
+            }
+        }
+        __syncthreads();
+        // ---- (B) L[i,kk] = S[i,kk] * Linv_kk^T for the tiles below the diagonal ----
+        for (int i = kk + 1 + warp; i < 8; i += NWARPS) {
+            double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                dmma884(c0, c1, D[(8 * i + fr) * LDD + 8 * kk + 4 * h + fk], I[(8 * kk + fr) * LDD + 8 * kk + 4 * h + fk]);
+            __syncwarp();
+            *reinterpret_cast<double2*>(D + (8 * i + fr) * LDD + 8 * kk + 2 * fk) = make_double2(c0, c1);
+        }
+        __syncthreads();
+        // ---- (C) S[i,j] -= L[i,kk] L[j,kk]^T, kk < j <= i; warp 0 takes the next diagonal tile only ----
+        {
+            const int n = 7 - kk;                         // tiles (i,j) with kk < j <= i < 8, enumerated row by row
+            int t = 0;
+            for (int i = kk + 1; i < 8; ++i)
+                for (int j = kk + 1; j <= i; ++j, ++t) {
+                    const int owner = t == 0 ? 0 : 1 + (t - 1) % (NWARPS - 1);
+                    if (owner != warp) continue;
+                    double2 c = *reinterpret_cast<const double2*>(D + (8 * i + fr) * LDD + 8 * j + 2 * fk);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+                        dmma884(c.x, c.y, -D[(8 * i + fr) * LDD + 8 * kk + 4 * h + fk], D[(8 * j + fr) * LDD + 8 * kk + 4 * h + fk]);
+                    *reinterpret_cast<double2*>(D + (8 * i + fr) * LDD + 8 * j + 2 * fk) = c;
+                }
+            (void)n;
+        }
+        // no CTA barrier here: the next (A) touches only tile (kk+1,kk+1), which warp 0 itself just updated
+    }
+    __syncthreads();
+    // ---- (D) inverse of the whole block: Linv[i,c] = -Linv_ii * sum_{p=c}^{i-1} L[i,p] Linv[p,c], warp c = block column ----
+    if (warp < 8) {
+        const int c = warp;
+        for (int i = c + 1; i < 8; ++i) {
+            double t0 = 0.0, t1 = 0.0;
+            for (int p = c; p < i; ++p)
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    dmma884(t0, t1, D[(8 * i + fr) * LDD + 8 * p + 4 * h + fk], I[(8 * p + 4 * h + fk) * LDD + 8 * c + fr]);
+            double* blk = I + (8 * i) * LDD + 8 * c;
+            *reinterpret_cast<double2*>(blk + fr * LDD + 2 * fk) = make_double2(t0, t1);
+            __syncwarp();
+            double r0 = 0.0, r1 = 0.0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                dmma884(r0, r1, -I[(8 * i + fr) * LDD + 8 * i + 4 * h + fk], blk[(4 * h + fk) * LDD + fr]);
+            __syncwarp();
+            *reinterpret_cast<double2*>(blk + fr * LDD + 2 * fk) = make_double2(r0, r1);
             __syncwarp();
         }
     }
@@ -292,15 +369,20 @@ __global__ void __launch_bounds__(THREADS, 2) factor_solve_kernel(SolveParams pr
                         for (int nb = 0; nb < 8; ++nb)
                             *reinterpret_cast<double2*>(Dsm + (16 * warp + 8 * i + fr) * LDD + nb * 8 + 2 * fk) =
                                 make_double2(-acc[i][nb][0], -acc[i][nb][1]);
+                } else if (active) {
+                    // park the raw strip in its final place so that no accumulator is live across the
+                    // factorisation of the diagonal block (it is re-read right after, from L1/L2)
+                    strip_store(acc, M + (long)mrow * ld + K, ld, lane);
                 }
                 __syncthreads();
                 factor_invert_block(Dsm, Ism, &bad_pivot, tid, lane, warp);
                 for (int e = tid; e < NB * NB; e += THREADS) {
                     const int r = e / NB, c = e % NB;
-                    M[(long)(K + r) * ld + K + c] = Ism[r * LDD + c];          // diagonal blocks hold L_jj^{-1}
+                    M[(long)(K + r) * ld + K + c] = c <= (r | 7) ? Ism[r * LDD + c] : 0.0;   // diagonal blocks hold L_jj^{-1}
                 }
                 __syncthreads();                                 // Dsm no longer needed: staging may reuse it
                 if (warp >= 4 && active) {
+                    strip_load(acc, M + (long)mrow * ld + K, ld, lane);
                     strip_times_tri<false>(acc, Ism, stage, lane);
                     strip_store(acc, M + (long)mrow * ld + K, ld, lane);
                 }

@@ -74,6 +74,33 @@ __global__ void dmma1688_kernel(double* out, int iters) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+
+// DFMA and DMMA issued by the same warp, interleaved: do the fp64 FMA pipe and the fp64 tensor sub-pipe overlap?
+template <int ILP, int FPM>
+__global__ void mixed_kernel(double* out, int iters) {
+    double c[ILP][2], f[ILP * FPM];
+    double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+#pragma unroll
+    for (int i = 0; i < ILP; ++i) { c[i][0] = i; c[i][1] = -i; }
+#pragma unroll
+    for (int i = 0; i < ILP * FPM; ++i) f[i] = threadIdx.x + i;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < ILP; ++i) {
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[i][0]), "+d"(c[i][1]) : "d"(a), "d"(b));
+#pragma unroll
+            for (int j = 0; j < FPM; ++j) f[i * FPM + j] = fma(f[i * FPM + j], b, a);
+        }
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < ILP; ++i) s += c[i][0] + c[i][1];
+#pragma unroll
+    for (int i = 0; i < ILP * FPM; ++i) s += f[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <typename F>
 static float time_ms(F launch) {
     cudaEvent_t e0, e1;
@@ -103,6 +130,16 @@ int main() {
         printf(", \"dmma884_tflops_t%d\": %.2f", threads, 2.0 * 256 * 8 * iters * (double)blocks * (threads / 32) / ms * 1e-9);
         ms = time_ms([&] { dmma1688_kernel<4><<<blocks, threads>>>(dout, iters); });
         printf(", \"dmma1688_tflops_t%d\": %.2f", threads, 2.0 * 1024 * 4 * iters * (double)blocks * (threads / 32) / ms * 1e-9);
+    }
+    {
+        const int threads = 512, blocks = sms * 4;
+        float ms = time_ms([&] { mixed_kernel<8, 4><<<blocks, threads>>>(dout, iters); });
+        // per warp and iteration: 8 DMMA (256 FMA each) + 8*4 DFMA x 32 lanes
+        printf(", \"mixed_dmma_plus_4dfma_tflops\": %.2f", 2.0 * (256 * 8 + 32 * 32) * iters * (double)blocks * (threads / 32) / ms * 1e-9);
+        ms = time_ms([&] { mixed_kernel<8, 8><<<blocks, threads>>>(dout, iters); });
+        printf(", \"mixed_dmma_plus_8dfma_tflops\": %.2f", 2.0 * (256 * 8 + 64 * 32) * iters * (double)blocks * (threads / 32) / ms * 1e-9);
+        ms = time_ms([&] { mixed_kernel<8, 2><<<blocks, threads>>>(dout, iters); });
+        printf(", \"mixed_dmma_plus_2dfma_tflops\": %.2f", 2.0 * (256 * 8 + 16 * 32) * iters * (double)blocks * (threads / 32) / ms * 1e-9);
     }
     CK(cudaDeviceSynchronize());
     printf("}\n");
