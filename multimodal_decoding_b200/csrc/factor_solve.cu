@@ -27,91 +27,93 @@ namespace {
 
 constexpr int THREADS = 288;          // 9 warps x 16 rows = 144 = EVAL_PAD
 constexpr int NWARPS = THREADS / 32;
-constexpr int KC = 16;                // k-values per pipeline chunk
-constexpr int STAGES = 3;
-constexpr int LDB_NT = 24;            // [n][k] chunk rows: 16 doubles + 8 pad (conflict-free 16-byte fragment loads)
+constexpr int KC = 8;                 // k-values per pipeline chunk (one 64-byte row segment)
+constexpr int STAGES = 4;
+constexpr int A_ROWS = NWARPS * 16;   // strip rows staged per chunk (one 16-row strip per warp)
+constexpr int A_STAGE = A_ROWS * KC;  // [row][k], 64-byte rows: conflict-free 16-byte fragment loads
 constexpr int LDB_NN = 66;            // [k][n] chunk rows: 64 doubles + 2 pad
-constexpr int STAGE_DOUBLES = 1632;   // >= 64*24, >= 16*66; 3 stages = 4896 doubles = 9 warps x 8 x 68 staging
+constexpr int STAGE_DOUBLES = A_STAGE + KC * LDB_NN;   // B is [n][k] (64 x 8) or [k][n] (8 x 66)
 constexpr int LDD = 68;               // stride of the 64x64 diagonal block and of the per-warp staging rows
 constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;
 static_assert(PIPE_DOUBLES >= NB * LDD, "diagonal block aliases the pipeline buffers");
 static_assert(PIPE_DOUBLES >= NWARPS * 8 * LDD, "strip staging aliases the pipeline buffers");
+static_assert(2 * THREADS == A_ROWS * (KC / 2) && 64 * (KC / 2) <= THREADS, "loader thread map");
 
 typedef double Acc[2][8][2];          // C fragments of a 16 x 64 strip: [row half][8-column block][2]
 
-// acc += strip(16 x 16*nchunks) * B^T   (NN = false: B rows are the 64 panel rows, contiguous along k)
-// acc += strip(16 x 16*nchunks) * B     (NN = true : B is (16*nchunks) x 64, row-major)
-// Every thread of the CTA must call this (cp.async staging and barriers are CTA-wide); `active`
-// says whether this warp owns a strip.  The k index inside a group of 8 is permuted the same way for
-// both operands (lane fk takes k = 8t + 2fk + p), which lets the strip operand use 16-byte loads.
-template <bool NN>
-__device__ __forceinline__ void strip_gemm(Acc& acc, const double* __restrict__ a_strip, long lda,
-                                           const double* __restrict__ b_src, long ldb, int nchunks,
-                                           double* pipe, bool active, int tid, int lane) {
+// acc += strip(16 x 8*nchunks) * B^T   (NN = false: B rows are the 64 panel rows, contiguous along k)
+// acc += strip(16 x 8*nchunks) * B     (NN = true : B is (8*nchunks) x 64, row-major)
+// Both operands go through a 4-stage cp.async ring: per chunk the nine strips (144 rows x 8 k-values) and
+// the shared B tile.  `a_row(r)` gives the global address of staged row r (r / 16 = warp that owns it) at
+// k = 0, or nullptr for an idle warp.  `init(acc)` runs after the first loads are in flight, so the
+// gather of the strip's initial value overlaps the pipeline fill.  Every thread of the CTA must call this
+// (staging and barriers are CTA-wide).  The k index inside a chunk is permuted the same way for both
+// operands (lane fk takes k = 2fk + p), which lets the fragments be 16-byte loads.
+template <bool NN, typename RowPtr, typename Init>
+__device__ __forceinline__ void strip_gemm(Acc& acc, RowPtr a_row, const double* __restrict__ b_src, long ldb,
+                                           int nchunks, double* pipe, bool active, Init init, int tid, int lane,
+                                           int warp) {
     const int fr = lane >> 2, fk = lane & 3;
-    auto load_b = [&](int stage, int c) {
+    const int lrow = tid >> 2, lpart = (tid & 3) * 2;
+    const double* a_src0 = a_row(lrow);
+    const double* a_src1 = a_row(lrow + THREADS / 4);
+    if (a_src0) a_src0 += lpart;
+    if (a_src1) a_src1 += lpart;
+    const int a_off0 = lrow * KC + lpart, a_off1 = a_off0 + (THREADS / 4) * KC;
+    const bool b_loader = tid < 64 * (KC / 2);
+    const double* b_ptr;
+    int b_off;
+    long b_step;
+    if (!NN) {
+        b_ptr = b_src + (long)lrow * ldb + lpart;
+        b_off = A_STAGE + lrow * KC + lpart;
+        b_step = KC;
+    } else {
+        const int kk = tid >> 5, n = (tid & 31) * 2;
+        b_ptr = b_src + (long)kk * ldb + n;
+        b_off = A_STAGE + kk * LDB_NN + n;
+        b_step = (long)KC * ldb;
+    }
+    auto load = [&](int stage, int c) {
         double* dst = pipe + stage * STAGE_DOUBLES;
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const int idx = tid + q * THREADS;
-            if (idx < 512) {
-                if (!NN) {
-                    const int n = idx >> 3, kk = (idx & 7) * 2;
-                    cp_async16(dst + n * LDB_NT + kk, b_src + (long)n * ldb + c * KC + kk);
-                } else {
-                    const int kk = idx >> 5, n = (idx & 31) * 2;
-                    cp_async16(dst + kk * LDB_NN + n, b_src + (long)(c * KC + kk) * ldb + n);
-                }
-            }
-        }
+        if (a_src0) cp_async16(dst + a_off0, a_src0 + c * KC);
+        if (a_src1) cp_async16(dst + a_off1, a_src1 + c * KC);
+        if (b_loader) cp_async16(dst + b_off, b_ptr + c * b_step);
     };
     __syncthreads();                                   // previous users of the pipeline buffers are done
     for (int s = 0; s < STAGES - 1; ++s) {
-        if (s < nchunks) load_b(s, s);
+        if (s < nchunks) load(s, s);
         cp_async_commit();
     }
-    const double* a0p = a_strip + (long)fr * lda + 2 * fk;
-    const double* a1p = a0p + 8 * lda;
-    double2 cur0, cur1, nxt0, nxt1;                   // strip operand, half a chunk (8 k-values) ahead
-    if (active && nchunks > 0) {
-        cur0 = *reinterpret_cast<const double2*>(a0p);
-        cur1 = *reinterpret_cast<const double2*>(a1p);
-    }
+    if (active) init(acc);
     for (int c = 0; c < nchunks; ++c) {
         cp_async_wait<STAGES - 2>();
         __syncthreads();
         {
             const int n = c + STAGES - 1;
-            if (n < nchunks) load_b(n % STAGES, n);
+            if (n < nchunks) load(n % STAGES, n);
             cp_async_commit();
         }
         if (active) {
-            const double* bs = pipe + (c % STAGES) * STAGE_DOUBLES;
+            const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
+            const double2 a0 = *reinterpret_cast<const double2*>(st + (warp * 16 + fr) * KC + 2 * fk);
+            const double2 a1 = *reinterpret_cast<const double2*>(st + (warp * 16 + 8 + fr) * KC + 2 * fk);
+            const double* bs = st + A_STAGE;
 #pragma unroll
-            for (int t = 0; t < 2; ++t) {
-                const int o = c * KC + 8 * (t + 1);
-                if (t == 0 || c + 1 < nchunks) {
-                    nxt0 = *reinterpret_cast<const double2*>(a0p + o);
-                    nxt1 = *reinterpret_cast<const double2*>(a1p + o);
+            for (int nb = 0; nb < 8; ++nb) {
+                double bx, by;
+                if (!NN) {
+                    const double2 b = *reinterpret_cast<const double2*>(bs + (nb * 8 + fr) * KC + 2 * fk);
+                    bx = b.x;
+                    by = b.y;
+                } else {
+                    bx = bs[(2 * fk) * LDB_NN + nb * 8 + fr];
+                    by = bs[(2 * fk + 1) * LDB_NN + nb * 8 + fr];
                 }
-#pragma unroll
-                for (int nb = 0; nb < 8; ++nb) {
-                    double bx, by;
-                    if (!NN) {
-                        const double2 b = *reinterpret_cast<const double2*>(bs + (nb * 8 + fr) * LDB_NT + 8 * t + 2 * fk);
-                        bx = b.x;
-                        by = b.y;
-                    } else {
-                        bx = bs[(8 * t + 2 * fk) * LDB_NN + nb * 8 + fr];
-                        by = bs[(8 * t + 2 * fk + 1) * LDB_NN + nb * 8 + fr];
-                    }
-                    dmma884(acc[0][nb][0], acc[0][nb][1], cur0.x, bx);
-                    dmma884(acc[1][nb][0], acc[1][nb][1], cur1.x, bx);
-                    dmma884(acc[0][nb][0], acc[0][nb][1], cur0.y, by);
-                    dmma884(acc[1][nb][0], acc[1][nb][1], cur1.y, by);
-                }
-                cur0 = nxt0;
-                cur1 = nxt1;
+                dmma884(acc[0][nb][0], acc[0][nb][1], a0.x, bx);
+                dmma884(acc[1][nb][0], acc[1][nb][1], a1.x, bx);
+                dmma884(acc[0][nb][0], acc[0][nb][1], a0.y, by);
+                dmma884(acc[1][nb][0], acc[1][nb][1], a1.y, by);
             }
         }
     }
@@ -357,8 +359,17 @@ __global__ void __launch_bounds__(THREADS, 2) factor_solve_kernel(SolveParams pr
             const bool active = u < n_strips;
             const bool is_eval = u >= n_a;
             const int mrow = is_eval ? kp + 16 * (u - n_a) : K + 16 * u;        // first row of the strip in M
-            if (active) strip_init(acc, task, prm, loc_sm, nbr_sm, is_eval, is_eval ? 16 * (u - n_a) : mrow, K, lane);
-            strip_gemm<false>(acc, M + (long)mrow * ld, ld, panel_rows, ld, K / KC, pipe, active, tid, lane);
+            // staged row r belongs to strip u0 + r / 16 of this round
+            auto a_row = [&](int r) -> const double* {
+                const int us = u0 + (r >> 4);
+                if (us >= n_strips) return nullptr;
+                const int row = us >= n_a ? kp + 16 * (us - n_a) : K + 16 * us;
+                return M + (long)(row + (r & 15)) * ld;
+            };
+            auto init = [&](Acc& a) {
+                strip_init(a, task, prm, loc_sm, nbr_sm, is_eval, is_eval ? 16 * (u - n_a) : mrow, K, lane);
+            };
+            strip_gemm<false>(acc, a_row, panel_rows, ld, K / KC, pipe, active, init, tid, lane, warp);
             if (u0 == 0) {
                 __syncthreads();                                 // pipeline buffers free -> diagonal block
                 if (warp < 4) {
@@ -408,7 +419,9 @@ __global__ void __launch_bounds__(THREADS, 2) factor_solve_kernel(SolveParams pr
                     acc[h][nb][0] = -w.x;
                     acc[h][nb][1] = -w.y;
                 }
-            strip_gemm<true>(acc, zrows + c0 + NB, ld, M + (long)(c0 + NB) * ld + c0, ld, Kb / KC, pipe, true, tid, lane);
+            auto a_row = [&](int r) -> const double* { return M + (long)(kp + r) * ld + c0 + NB; };
+            strip_gemm<true>(acc, a_row, M + (long)(c0 + NB) * ld + c0, ld, Kb / KC, pipe, true, [](Acc&) {}, tid, lane,
+                             warp);
             __syncthreads();                                     // pipeline idle, previous Ism readers done
             for (int e = tid; e < NB * NB; e += THREADS) {
                 const int r = e / NB, c = e % NB;
