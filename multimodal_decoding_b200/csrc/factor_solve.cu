@@ -1,5 +1,5 @@
 // Per-centre ridge solve in float64 (the part sklearn delegates to LAPACK dposv, `_ridge.py`
-// _solve_cholesky, reached from searchlight.py:56-59), one CTA per centre, two CTAs per SM:
+// _solve_cholesky, reached from searchlight.py:56-59), one 4-warp CTA per centre, three CTAs per SM:
 //
 //   A  = G[loc, loc] + alpha I            (k x k, read straight out of the cluster's union Gram)
 //   A  = L L^T                            blocked left-looking Cholesky, 64-wide panels
@@ -7,52 +7,58 @@
 //
 // Only the 143 evaluation rows are ever multiplied by the ridge weights
 // (predictions = X_eval W = (X_eval A^{-1}) (X_nbh^T Y)), so the solve runs on 144 right-hand
-// sides instead of the D columns of X^T Y.  E is appended below A as extra 16-row strips: the
+// sides instead of the D columns of X^T Y.  E is appended below A as nine extra 16-row strips: the
 // panel update that produces L also yields the forward solve W = E L^{-T}; the backward solve
-// Zt = W L^{-1} runs afterwards, one warp per strip.
+// Zt = W L^{-1} runs afterwards on the same strips.
 //
-// Work decomposition.  A "strip" is 16 rows x 64 columns of the current panel, owned by one
-// warp: acc(16x64) = init - strip(16xK) * panel(64xK)^T on the fp64 tensor pipe (DMMA m8n8k4).
-// The panel operand (shared by all nine warps) is staged in shared memory with a 3-stage cp.async
-// pipeline, the strip operand streams from global/L2 with 16-byte loads one chunk ahead.  The
-// initial value of a strip is gathered from the union Gram (or the evaluation trials) at that
-// moment, so A itself is never materialised.  The triangular solve against the 64x64 diagonal
-// block is a product with its inverse (kept in shared memory), applied to the strip while it is
-// still on chip; every strip of L / W is written to global memory exactly once.
+// Work decomposition.  A "strip" is 16 rows x 64 columns of the current panel:
+//   acc(16x64) = init - strip(16xK) * panel(64xK)^T      on the fp64 tensor pipe (DMMA m8n8k4).
+// A round handles four strips, one per warp (one warp per SM sub-partition, so the four schedulers
+// carry the same load); both operands of the round go through a 4-stage cp.async ring in shared
+// memory.  The number of strips of a panel is always 4q + 1: the last one is processed by all four
+// warps together, 16 columns each ("split" round), so no warp idles.  The initial value of a strip
+// is gathered from the union Gram (or the evaluation trials) while the ring fills, so A itself is
+// never materialised.  The triangular solve against the 64x64 diagonal block is a product with its
+// inverse (kept in shared memory), applied to the strip while it is still on chip; every strip of
+// L / W is written to global memory exactly once.
 #include "common.cuh"
 #include "kernels.h"
 
 namespace mmd {
 namespace {
 
-constexpr int THREADS = 288;          // 9 warps x 16 rows = 144 = EVAL_PAD
+constexpr int THREADS = 128;
 constexpr int NWARPS = THREADS / 32;
 constexpr int KC = 8;                 // k-values per pipeline chunk (one 64-byte row segment)
 constexpr int STAGES = 4;
 constexpr int A_ROWS = NWARPS * 16;   // strip rows staged per chunk (one 16-row strip per warp)
 constexpr int A_STAGE = A_ROWS * KC;  // [row][k], 64-byte rows: conflict-free 16-byte fragment loads
 constexpr int LDB_NN = 66;            // [k][n] chunk rows: 64 doubles + 2 pad
-constexpr int STAGE_DOUBLES = A_STAGE + KC * LDB_NN;   // B is [n][k] (64 x 8) or [k][n] (8 x 66)
-constexpr int LDD = 68;               // stride of the 64x64 diagonal block and of the per-warp staging rows
-constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;
-static_assert(PIPE_DOUBLES >= NB * LDD, "diagonal block aliases the pipeline buffers");
-static_assert(PIPE_DOUBLES >= NWARPS * 8 * LDD, "strip staging aliases the pipeline buffers");
-static_assert(2 * THREADS == A_ROWS * (KC / 2) && 64 * (KC / 2) <= THREADS, "loader thread map");
+constexpr int LDD = 68;               // stride of the 64x64 diagonal block and of the staging rows
+constexpr int STAGE_DOUBLES = NB * LDD / STAGES;       // 1088 >= A_STAGE + max(64*KC, KC*LDB_NN)
+constexpr int PIPE_DOUBLES = STAGES * STAGE_DOUBLES;   // = NB * LDD: the diagonal block aliases the ring
+static_assert(STAGE_DOUBLES >= A_STAGE + KC * LDB_NN && STAGE_DOUBLES >= A_STAGE + NB * KC, "stage size");
+static_assert(PIPE_DOUBLES >= NWARPS * 8 * LDD && PIPE_DOUBLES >= 16 * LDD, "strip staging aliases the ring");
+static_assert(A_ROWS * (KC / 2) == 2 * THREADS && NB * (KC / 2) == 2 * THREADS, "loader thread map");
+static_assert(EVAL_PAD % 16 == 0 && (EVAL_PAD / 16) % NWARPS == 1, "strip count of a panel must be 4q + 1");
 
-typedef double Acc[2][8][2];          // C fragments of a 16 x 64 strip: [row half][8-column block][2]
+// C fragments of a 16-row strip: [row half][8-column block][2]; NBW = 8 (whole strip) or 2 (16 columns)
+template <int NBW>
+struct Frag {
+    double v[2][NBW][2];
+};
 
 // acc += strip(16 x 8*nchunks) * B^T   (NN = false: B rows are the 64 panel rows, contiguous along k)
 // acc += strip(16 x 8*nchunks) * B     (NN = true : B is (8*nchunks) x 64, row-major)
-// Both operands go through a 4-stage cp.async ring: per chunk the nine strips (144 rows x 8 k-values) and
-// the shared B tile.  `a_row(r)` gives the global address of staged row r (r / 16 = warp that owns it) at
-// k = 0, or nullptr for an idle warp.  `init(acc)` runs after the first loads are in flight, so the
-// gather of the strip's initial value overlaps the pipeline fill.  Every thread of the CTA must call this
-// (staging and barriers are CTA-wide).  The k index inside a chunk is permuted the same way for both
-// operands (lane fk takes k = 2fk + p), which lets the fragments be 16-byte loads.
-template <bool NN, typename RowPtr, typename Init>
-__device__ __forceinline__ void strip_gemm(Acc& acc, RowPtr a_row, const double* __restrict__ b_src, long ldb,
-                                           int nchunks, double* pipe, bool active, Init init, int tid, int lane,
-                                           int warp) {
+// NBW = 8: warp w owns staged strip w and all 64 columns.  NBW = 2: all warps share staged strip 0 and
+// warp w owns columns 16w .. 16w+15.  `a_row(r)` gives the global address of staged row r at k = 0
+// (nullptr: row not staged).  `init()` runs after the first loads are in flight, so the gather of the
+// strip's initial value overlaps the pipeline fill.  Every thread of the CTA must call this (staging
+// and barriers are CTA-wide).  The k index inside a chunk is permuted the same way for both operands
+// (lane fk takes k = 2fk + p), which lets the fragments be 16-byte loads.
+template <bool NN, int NBW, typename RowPtr, typename Init>
+__device__ __forceinline__ void strip_gemm(Frag<NBW>& acc, RowPtr a_row, const double* __restrict__ b_src, long ldb,
+                                           int nchunks, double* pipe, Init init, int tid, int lane, int warp) {
     const int fr = lane >> 2, fk = lane & 3;
     const int lrow = tid >> 2, lpart = (tid & 3) * 2;
     const double* a_src0 = a_row(lrow);
@@ -60,32 +66,37 @@ __device__ __forceinline__ void strip_gemm(Acc& acc, RowPtr a_row, const double*
     if (a_src0) a_src0 += lpart;
     if (a_src1) a_src1 += lpart;
     const int a_off0 = lrow * KC + lpart, a_off1 = a_off0 + (THREADS / 4) * KC;
-    const bool b_loader = tid < 64 * (KC / 2);
-    const double* b_ptr;
-    int b_off;
+    const double *b_ptr0, *b_ptr1;
+    int b_off0, b_off1;
     long b_step;
     if (!NN) {
-        b_ptr = b_src + (long)lrow * ldb + lpart;
-        b_off = A_STAGE + lrow * KC + lpart;
+        b_ptr0 = b_src + (long)lrow * ldb + lpart;
+        b_ptr1 = b_ptr0 + (long)(THREADS / 4) * ldb;
+        b_off0 = A_STAGE + lrow * KC + lpart;
+        b_off1 = b_off0 + (THREADS / 4) * KC;
         b_step = KC;
     } else {
         const int kk = tid >> 5, n = (tid & 31) * 2;
-        b_ptr = b_src + (long)kk * ldb + n;
-        b_off = A_STAGE + kk * LDB_NN + n;
+        b_ptr0 = b_src + (long)kk * ldb + n;
+        b_ptr1 = b_ptr0 + (long)(KC / 2) * ldb;
+        b_off0 = A_STAGE + kk * LDB_NN + n;
+        b_off1 = b_off0 + (KC / 2) * LDB_NN;
         b_step = (long)KC * ldb;
     }
     auto load = [&](int stage, int c) {
         double* dst = pipe + stage * STAGE_DOUBLES;
         if (a_src0) cp_async16(dst + a_off0, a_src0 + c * KC);
         if (a_src1) cp_async16(dst + a_off1, a_src1 + c * KC);
-        if (b_loader) cp_async16(dst + b_off, b_ptr + c * b_step);
+        cp_async16(dst + b_off0, b_ptr0 + c * b_step);
+        cp_async16(dst + b_off1, b_ptr1 + c * b_step);
     };
     __syncthreads();                                   // previous users of the pipeline buffers are done
     for (int s = 0; s < STAGES - 1; ++s) {
         if (s < nchunks) load(s, s);
         cp_async_commit();
     }
-    if (active) init(acc);
+    init();
+    const int a_slot = NBW == 8 ? warp : 0, nb0 = NBW == 8 ? 0 : warp * NBW;
     for (int c = 0; c < nchunks; ++c) {
         cp_async_wait<STAGES - 2>();
         __syncthreads();
@@ -94,26 +105,35 @@ __device__ __forceinline__ void strip_gemm(Acc& acc, RowPtr a_row, const double*
             if (n < nchunks) load(n % STAGES, n);
             cp_async_commit();
         }
-        if (active) {
-            const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
-            const double2 a0 = *reinterpret_cast<const double2*>(st + (warp * 16 + fr) * KC + 2 * fk);
-            const double2 a1 = *reinterpret_cast<const double2*>(st + (warp * 16 + 8 + fr) * KC + 2 * fk);
-            const double* bs = st + A_STAGE;
+        const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
+        const double2 a0 = *reinterpret_cast<const double2*>(st + (a_slot * 16 + fr) * KC + 2 * fk);
+        const double2 a1 = *reinterpret_cast<const double2*>(st + (a_slot * 16 + 8 + fr) * KC + 2 * fk);
+        const double* bs = st + A_STAGE;
 #pragma unroll
-            for (int nb = 0; nb < 8; ++nb) {
-                double bx, by;
+        for (int q = 0; q < NBW; q += 2) {
+            double bx[2], by[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int nb = nb0 + q + e;
                 if (!NN) {
                     const double2 b = *reinterpret_cast<const double2*>(bs + (nb * 8 + fr) * KC + 2 * fk);
-                    bx = b.x;
-                    by = b.y;
+                    bx[e] = b.x;
+                    by[e] = b.y;
                 } else {
-                    bx = bs[(2 * fk) * LDB_NN + nb * 8 + fr];
-                    by = bs[(2 * fk + 1) * LDB_NN + nb * 8 + fr];
+                    bx[e] = bs[(2 * fk) * LDB_NN + nb * 8 + fr];
+                    by[e] = bs[(2 * fk + 1) * LDB_NN + nb * 8 + fr];
                 }
-                dmma884(acc[0][nb][0], acc[0][nb][1], a0.x, bx);
-                dmma884(acc[1][nb][0], acc[1][nb][1], a1.x, bx);
-                dmma884(acc[0][nb][0], acc[0][nb][1], a0.y, by);
-                dmma884(acc[1][nb][0], acc[1][nb][1], a1.y, by);
+            }
+            // four independent accumulators between dependent DMMAs
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                dmma884(acc.v[0][q + e][0], acc.v[0][q + e][1], a0.x, bx[e]);
+                dmma884(acc.v[1][q + e][0], acc.v[1][q + e][1], a1.x, bx[e]);
+            }
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                dmma884(acc.v[0][q + e][0], acc.v[0][q + e][1], a0.y, by[e]);
+                dmma884(acc.v[1][q + e][0], acc.v[1][q + e][1], a1.y, by[e]);
             }
         }
     }
@@ -125,15 +145,15 @@ __device__ __forceinline__ void strip_gemm(Acc& acc, RowPtr a_row, const double*
 // shared memory (stride LDD).  The strip is staged through a warp-private shared buffer, 8 rows at a
 // time, to turn C fragments into A fragments; zero blocks of T are skipped.
 template <bool NN>
-__device__ __forceinline__ void strip_times_tri(Acc& acc, const double* __restrict__ T, double* stage, int lane) {
+__device__ __forceinline__ void strip_times_tri(Frag<8>& acc, const double* __restrict__ T, double* stage, int lane) {
     const int fr = lane >> 2, fk = lane & 3;
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
         __syncwarp();
 #pragma unroll
         for (int nb = 0; nb < 8; ++nb) {
-            *reinterpret_cast<double2*>(stage + fr * LDD + nb * 8 + 2 * fk) = make_double2(-acc[i][nb][0], -acc[i][nb][1]);
-            acc[i][nb][0] = acc[i][nb][1] = 0.0;
+            *reinterpret_cast<double2*>(stage + fr * LDD + nb * 8 + 2 * fk) = make_double2(-acc.v[i][nb][0], -acc.v[i][nb][1]);
+            acc.v[i][nb][0] = acc.v[i][nb][1] = 0.0;
         }
         __syncwarp();
 #pragma unroll 1
@@ -147,9 +167,9 @@ __device__ __forceinline__ void strip_times_tri(Acc& acc, const double* __restri
                     // NT: out[r][n] = sum_c P[r][c] T[n][c], T[n][c] = 0 for c > n  -> k-step ks feeds blocks nb >= ks/2
                     // NN: out[r][n] = sum_c P[r][c] T[c][n], T[c][n] = 0 for c < n  -> k-step ks feeds blocks nb <= ks/2
                     if (!NN) {
-                        if (nb >= kb) dmma884(acc[i][nb][0], acc[i][nb][1], a, T[(nb * 8 + fr) * LDD + 4 * ks + fk]);
+                        if (nb >= kb) dmma884(acc.v[i][nb][0], acc.v[i][nb][1], a, T[(nb * 8 + fr) * LDD + 4 * ks + fk]);
                     } else {
-                        if (nb <= kb) dmma884(acc[i][nb][0], acc[i][nb][1], a, T[(4 * ks + fk) * LDD + nb * 8 + fr]);
+                        if (nb <= kb) dmma884(acc.v[i][nb][0], acc.v[i][nb][1], a, T[(4 * ks + fk) * LDD + nb * 8 + fr]);
                     }
                 }
             }
@@ -157,58 +177,99 @@ __device__ __forceinline__ void strip_times_tri(Acc& acc, const double* __restri
     }
 }
 
-// Negated initial value of a strip of the current panel: -(G[loc, loc] + alpha I) for rows of A,
-// -E for the evaluation rows (u >= n_a_strips).
-__device__ __forceinline__ void strip_init(Acc& acc, const CentreTask& task, const SolveParams& prm, const int* loc_sm,
-                                           const int* nbr_sm, bool is_eval, int row0, int col0, int lane) {
+// Same product for the strip of a split round: every warp holds 16 of the 64 columns.  The raw strip is
+// assembled in shared memory (S, 16 x LDD, aliases the idle pipeline ring), then warp w computes output
+// columns 16w .. 16w+15.
+template <bool NN>
+__device__ __forceinline__ void split_times_tri(Frag<2>& acc, const double* __restrict__ T, double* S, int lane, int warp) {
+    const int fr = lane >> 2, fk = lane & 3;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            *reinterpret_cast<double2*>(S + (8 * i + fr) * LDD + (2 * warp + e) * 8 + 2 * fk) =
+                make_double2(-acc.v[i][e][0], -acc.v[i][e][1]);
+            acc.v[i][e][0] = acc.v[i][e][1] = 0.0;
+        }
+    __syncthreads();
+#pragma unroll 4
+    for (int ks = 0; ks < 16; ++ks) {
+        const int kb = ks >> 1;
+        const double a0 = S[fr * LDD + 4 * ks + fk], a1 = S[(8 + fr) * LDD + 4 * ks + fk];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int nb = 2 * warp + e;
+            if (!NN ? nb >= kb : nb <= kb) {
+                const double b = !NN ? T[(nb * 8 + fr) * LDD + 4 * ks + fk] : T[(4 * ks + fk) * LDD + nb * 8 + fr];
+                dmma884(acc.v[0][e][0], acc.v[0][e][1], a0, b);
+                dmma884(acc.v[1][e][0], acc.v[1][e][1], a1, b);
+            }
+        }
+    }
+}
+
+// Negated initial value of NBW column blocks of a strip of the current panel, starting at column col0:
+// -(G[loc, loc] + alpha I) for rows of A, -E for the evaluation rows.
+template <int NBW>
+__device__ __forceinline__ void strip_init(Frag<NBW>& acc, const CentreTask& task, const SolveParams& prm, bool is_eval,
+                                           int row0, int col0, int lane) {
     const int fr = lane >> 2, fk = lane & 3;
     const int k = prm.k;
+    int lj[NBW][2], vj[NBW][2];
+#pragma unroll
+    for (int nb = 0; nb < NBW; ++nb)
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int c = col0 + nb * 8 + 2 * fk + q;
+            lj[nb][q] = c < k ? __ldg((is_eval ? task.nbr : task.loc) + c) : -1;
+            vj[nb][q] = c;
+        }
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
         const int r = row0 + 8 * i + fr;                 // row of A, or evaluation trial index
-        const int li = is_eval ? 0 : loc_sm[r];
+        const int li = is_eval ? 0 : (r < k ? __ldg(task.loc + r) : -1);
 #pragma unroll
-        for (int nb = 0; nb < 8; ++nb)
+        for (int nb = 0; nb < NBW; ++nb)
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
-                const int c = col0 + nb * 8 + 2 * fk + q;
+                const int l = lj[nb][q];
                 double v;
                 if (is_eval) {
-                    v = c < k ? h2d(prm.Xe[(long)nbr_sm[c] * EVAL_PAD + r]) : 0.0;
+                    v = l >= 0 ? h2d(prm.Xe[(long)l * EVAL_PAD + r]) : 0.0;
+                } else if (li >= 0 && l >= 0) {
+                    const int hi = li > l ? li : l, lo = li > l ? l : li;
+                    v = task.gram[(long)hi * task.gram_ld + lo];
+                    if (r == vj[nb][q]) v += prm.alpha;
                 } else {
-                    const int lj = loc_sm[c];
-                    if (li >= 0 && lj >= 0) {
-                        const int hi = li > lj ? li : lj, lo = li > lj ? lj : li;
-                        v = task.gram[(long)hi * task.gram_ld + lo];
-                        if (r == c) v += prm.alpha;
-                    } else {
-                        v = (r == c) ? 1.0 : 0.0;        // padding rows/columns: identity
-                    }
+                    v = (r == vj[nb][q]) ? 1.0 : 0.0;    // padding rows/columns: identity
                 }
-                acc[i][nb][q] = -v;
+                acc.v[i][nb][q] = -v;
             }
     }
 }
 
-__device__ __forceinline__ void strip_store(const Acc& acc, double* dst, long ld, int lane) {
+template <int NBW>
+__device__ __forceinline__ void strip_store(const Frag<NBW>& acc, double* dst, long ld, int lane) {
     const int fr = lane >> 2, fk = lane & 3;
 #pragma unroll
     for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int nb = 0; nb < 8; ++nb)
+        for (int nb = 0; nb < NBW; ++nb)
             *reinterpret_cast<double2*>(dst + (long)(8 * i + fr) * ld + nb * 8 + 2 * fk) =
-                make_double2(acc[i][nb][0], acc[i][nb][1]);
+                make_double2(acc.v[i][nb][0], acc.v[i][nb][1]);
 }
 
-__device__ __forceinline__ void strip_load(Acc& acc, const double* src, long ld, int lane) {
+// acc = -src
+template <int NBW>
+__device__ __forceinline__ void strip_load_neg(Frag<NBW>& acc, const double* src, long ld, int lane) {
     const int fr = lane >> 2, fk = lane & 3;
 #pragma unroll
     for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int nb = 0; nb < 8; ++nb) {
+        for (int nb = 0; nb < NBW; ++nb) {
             const double2 v = *reinterpret_cast<const double2*>(src + (long)(8 * i + fr) * ld + nb * 8 + 2 * fk);
-            acc[i][nb][0] = v.x;
-            acc[i][nb][1] = v.y;
+            acc.v[i][nb][0] = -v.x;
+            acc.v[i][nb][1] = -v.y;
         }
 }
 
@@ -218,7 +279,7 @@ __device__ __forceinline__ void strip_load(Acc& acc, const double* src, long ld,
 //   (A) warp 0 factors and inverts the diagonal tile in registers (one row per lane, shuffles only),
 //   (B) the tiles below it are multiplied by that inverse, (C) the trailing tiles get their rank-8 update,
 // (B) and (C) on the DMMA pipe with fragments read straight from shared memory; (D) builds the inverse of
-// the whole block by block forward substitution, one block column per warp.
+// the whole block by block forward substitution, block columns dealt to the warps.
 __device__ __forceinline__ void factor_invert_block(double* D, double* I, int* bad_pivot, int tid, int lane, int warp) {
     const int fr = lane >> 2, fk = lane & 3;
     for (int kk = 0; kk < 8; ++kk) {
@@ -297,8 +358,8 @@ __device__ __forceinline__ void factor_invert_block(double* D, double* I, int* b
     }
     __syncthreads();
     // ---- (D) inverse of the whole block: Linv[i,c] = -Linv_ii * sum_{p=c}^{i-1} L[i,p] Linv[p,c], warp c = block column ----
-    if (warp < 8) {
-        const int c = warp;
+    for (int c = warp; c < 8; c += NWARPS) {
+
         for (int i = c + 1; i < 8; ++i) {
             double t0 = 0.0, t1 = 0.0;
             for (int p = c; p < i; ++p)
@@ -320,118 +381,100 @@ __device__ __forceinline__ void factor_invert_block(double* D, double* I, int* b
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(THREADS, 2) factor_solve_kernel(SolveParams prm) {
+__global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams prm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* pipe = reinterpret_cast<double*>(smem_raw);         // cp.async stages | diagonal block | strip staging
+    double* pipe = reinterpret_cast<double*>(smem_raw);         // cp.async ring | diagonal block | strip staging
     double* Ism = pipe + PIPE_DOUBLES;                          // NB x LDD: L_jj^{-1}
-    int* loc_sm = reinterpret_cast<int*>(Ism + NB * LDD);       // kp
-    int* nbr_sm = loc_sm + prm.kp;                              // kp
     __shared__ int bad_pivot;
 
     const int task_id = blockIdx.x;
     if (task_id >= prm.n_tasks) return;
     const CentreTask task = prm.tasks[task_id];
-    const int k = prm.k, kp = prm.kp, nblk = kp / NB;
+    const int kp = prm.kp, nblk = kp / NB;
     const long ld = kp;
     double* M = prm.work + (long)task_id * (kp + EVAL_PAD) * ld;   // rows 0..kp-1: L ; rows kp..: W then Zt
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double* stage = pipe + warp * 8 * LDD;
     double* Dsm = pipe;
+    constexpr int N_ESTRIPS = EVAL_PAD / 16;
 
     if (tid == 0) bad_pivot = 0;
-    for (int i = tid; i < kp; i += THREADS) {
-        loc_sm[i] = i < k ? task.loc[i] : -1;
-        nbr_sm[i] = i < k ? task.nbr[i] : 0;
-    }
-    __syncthreads();
-
-    Acc acc;
-    constexpr int N_ESTRIPS = EVAL_PAD / 16;
 
     // ---------------- factorisation + forward solve, panel by panel ----------------
     for (int j = 0; j < nblk; ++j) {
         const int K = j * NB;
         const int n_a = kp / 16 - 4 * j;                        // strips of A from the diagonal block down
-        const int n_strips = n_a + N_ESTRIPS;
+        const int n_strips = n_a + N_ESTRIPS;                   // = 4q + 1
         const double* panel_rows = M + (long)K * ld;            // L[K..K+63][0..K)
-        for (int u0 = 0; u0 < n_strips; u0 += NWARPS) {
+        auto strip_row = [&](int u) { return u >= n_a ? kp + 16 * (u - n_a) : K + 16 * u; };   // first row in M
+
+        for (int u0 = 0; u0 + NWARPS <= n_strips; u0 += NWARPS) {
             const int u = u0 + warp;
-            const bool active = u < n_strips;
             const bool is_eval = u >= n_a;
-            const int mrow = is_eval ? kp + 16 * (u - n_a) : K + 16 * u;        // first row of the strip in M
-            // staged row r belongs to strip u0 + r / 16 of this round
-            auto a_row = [&](int r) -> const double* {
-                const int us = u0 + (r >> 4);
-                if (us >= n_strips) return nullptr;
-                const int row = us >= n_a ? kp + 16 * (us - n_a) : K + 16 * us;
-                return M + (long)(row + (r & 15)) * ld;
-            };
-            auto init = [&](Acc& a) {
-                strip_init(a, task, prm, loc_sm, nbr_sm, is_eval, is_eval ? 16 * (u - n_a) : mrow, K, lane);
-            };
-            strip_gemm<false>(acc, a_row, panel_rows, ld, K / KC, pipe, active, init, tid, lane, warp);
+            const int mrow = strip_row(u);
+            Frag<8> acc;
+            auto a_row = [&](int r) -> const double* { return M + (long)(strip_row(u0 + (r >> 4)) + (r & 15)) * ld; };
+            auto init = [&]() { strip_init<8>(acc, task, prm, is_eval, is_eval ? mrow - kp : mrow, K, lane); };
+            strip_gemm<false, 8>(acc, a_row, panel_rows, ld, K / KC, pipe, init, tid, lane, warp);
             if (u0 == 0) {
-                __syncthreads();                                 // pipeline buffers free -> diagonal block
-                if (warp < 4) {
-                    const int fr = lane >> 2, fk = lane & 3;
+                // the four strips of the diagonal block: factor it, keep its inverse
+                const int fr = lane >> 2, fk = lane & 3;
 #pragma unroll
-                    for (int i = 0; i < 2; ++i)
+                for (int i = 0; i < 2; ++i)
 #pragma unroll
-                        for (int nb = 0; nb < 8; ++nb)
-                            *reinterpret_cast<double2*>(Dsm + (16 * warp + 8 * i + fr) * LDD + nb * 8 + 2 * fk) =
-                                make_double2(-acc[i][nb][0], -acc[i][nb][1]);
-                } else if (active) {
-                    // park the raw strip in its final place so that no accumulator is live across the
-                    // factorisation of the diagonal block (it is re-read right after, from L1/L2)
-                    strip_store(acc, M + (long)mrow * ld + K, ld, lane);
-                }
+                    for (int nb = 0; nb < 8; ++nb)
+                        *reinterpret_cast<double2*>(Dsm + (16 * warp + 8 * i + fr) * LDD + nb * 8 + 2 * fk) =
+                            make_double2(-acc.v[i][nb][0], -acc.v[i][nb][1]);
                 __syncthreads();
                 factor_invert_block(Dsm, Ism, &bad_pivot, tid, lane, warp);
                 for (int e = tid; e < NB * NB; e += THREADS) {
                     const int r = e / NB, c = e % NB;
                     M[(long)(K + r) * ld + K + c] = c <= (r | 7) ? Ism[r * LDD + c] : 0.0;   // diagonal blocks hold L_jj^{-1}
                 }
-                __syncthreads();                                 // Dsm no longer needed: staging may reuse it
-                if (warp >= 4 && active) {
-                    strip_load(acc, M + (long)mrow * ld + K, ld, lane);
-                    strip_times_tri<false>(acc, Ism, stage, lane);
-                    strip_store(acc, M + (long)mrow * ld + K, ld, lane);
-                }
-            } else if (active) {
+            } else {
                 strip_times_tri<false>(acc, Ism, stage, lane);
-                strip_store(acc, M + (long)mrow * ld + K, ld, lane);
+                strip_store<8>(acc, M + (long)mrow * ld + K, ld, lane);
             }
+        }
+        {   // split round: the last evaluation strip, 16 columns per warp
+            const int mrow = strip_row(n_strips - 1);
+            Frag<2> acc;
+            auto a_row = [&](int r) -> const double* { return r < 16 ? M + (long)(mrow + r) * ld : nullptr; };
+            auto init = [&]() { strip_init<2>(acc, task, prm, true, mrow - kp, K + 16 * warp, lane); };
+            strip_gemm<false, 2>(acc, a_row, panel_rows, ld, K / KC, pipe, init, tid, lane, warp);
+            split_times_tri<false>(acc, Ism, pipe, lane, warp);
+            strip_store<2>(acc, M + (long)mrow * ld + K + 16 * warp, ld, lane);
         }
         __syncthreads();                                         // panel j complete (global writes visible CTA-wide)
     }
 
-    // ---------------- backward solve: Zt_i = (W_i - sum_{p>i} Zt_p L_pi) L_ii^{-1}, one warp per 16 rows ----------------
-    {
-        double* zrows = M + (long)(kp + 16 * warp) * ld;
-        const int fr = lane >> 2, fk = lane & 3;
-        for (int i = nblk - 1; i >= 0; --i) {
-            const int c0 = i * NB, Kb = kp - (c0 + NB);
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-#pragma unroll
-                for (int nb = 0; nb < 8; ++nb) {
-                    const double2 w = *reinterpret_cast<const double2*>(zrows + (long)(8 * h + fr) * ld + c0 + nb * 8 + 2 * fk);
-                    acc[h][nb][0] = -w.x;
-                    acc[h][nb][1] = -w.y;
-                }
-            auto a_row = [&](int r) -> const double* { return M + (long)(kp + r) * ld + c0 + NB; };
-            strip_gemm<true>(acc, a_row, M + (long)(c0 + NB) * ld + c0, ld, Kb / KC, pipe, true, [](Acc&) {}, tid, lane,
-                             warp);
-            __syncthreads();                                     // pipeline idle, previous Ism readers done
-            for (int e = tid; e < NB * NB; e += THREADS) {
-                const int r = e / NB, c = e % NB;
-                Ism[r * LDD + c] = M[(long)(c0 + r) * ld + c0 + c];
-            }
-            __syncthreads();
-            strip_times_tri<true>(acc, Ism, stage, lane);
-            strip_store(acc, zrows + c0, ld, lane);
-            __syncthreads();                                     // Zt block visible before it is read as an operand
+    // ---------------- backward solve: Zt_i = (W_i - sum_{p>i} Zt_p L_pi) L_ii^{-1} ----------------
+    for (int i = nblk - 1; i >= 0; --i) {
+        const int c0 = i * NB, Kb = kp - (c0 + NB);
+        const double* lpanel = M + (long)(c0 + NB) * ld + c0;   // L[c0+64.., c0..c0+63], row-major (k x n)
+        for (int e = tid; e < NB * NB; e += THREADS) {           // previous readers of Ism passed a barrier
+            const int r = e / NB, c = e % NB;
+            Ism[r * LDD + c] = M[(long)(c0 + r) * ld + c0 + c];
         }
+        for (int u0 = 0; u0 + NWARPS <= N_ESTRIPS; u0 += NWARPS) {
+            double* zrows = M + (long)(kp + 16 * (u0 + warp)) * ld;
+            Frag<8> acc;
+            auto a_row = [&](int r) -> const double* { return M + (long)(kp + 16 * u0 + r) * ld + c0 + NB; };
+            auto init = [&]() { strip_load_neg<8>(acc, zrows + c0, ld, lane); };
+            strip_gemm<true, 8>(acc, a_row, lpanel, ld, Kb / KC, pipe, init, tid, lane, warp);
+            strip_times_tri<true>(acc, Ism, stage, lane);
+            strip_store<8>(acc, zrows + c0, ld, lane);
+        }
+        {
+            double* zrows = M + (long)(kp + 16 * (N_ESTRIPS - 1)) * ld;
+            Frag<2> acc;
+            auto a_row = [&](int r) -> const double* { return r < 16 ? zrows + (long)r * ld + c0 + NB : nullptr; };
+            auto init = [&]() { strip_load_neg<2>(acc, zrows + c0 + 16 * warp, ld, lane); };
+            strip_gemm<true, 2>(acc, a_row, lpanel, ld, Kb / KC, pipe, init, tid, lane, warp);
+            split_times_tri<true>(acc, Ism, pipe, lane, warp);
+            strip_store<2>(acc, zrows + c0 + 16 * warp, ld, lane);
+        }
+        __syncthreads();                                         // Zt block visible before it is read as an operand
     }
     if (tid == 0) prm.flags[task.centre] = bad_pivot;
 }
@@ -441,13 +484,16 @@ __global__ void __launch_bounds__(THREADS, 2) factor_solve_kernel(SolveParams pr
 size_t factor_solve_smem_bytes() { return (size_t)(PIPE_DOUBLES + NB * LDD) * sizeof(double); }
 
 cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s) {
-    const size_t smem = factor_solve_smem_bytes() + 2 * (size_t)p.kp * sizeof(int);
-    static size_t configured = 0;
-    if (smem > configured) {
+    const size_t smem = factor_solve_smem_bytes();
+    static bool configured = false;
+    if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(factor_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured = smem;
+        e = cudaFuncSetAttribute(factor_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (e != cudaSuccess) return e;
+        configured = true;
     }
+    if (p.kp % NB != 0) return cudaErrorInvalidValue;
     factor_solve_kernel<<<p.n_tasks, THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
