@@ -48,6 +48,8 @@ def parse_args():
                    help="weak: every GPU runs one whole hemisphere job per step (configs[4] distributes whole "
                         "searchlights); strong: ONE hemisphere, centres sharded across the GPUs")
     p.add_argument("--cpu-centres", type=int, default=48, help="centres of the CPU-baseline sample")
+    p.add_argument("--batch-centres", type=int, default=0, help="engine knob: centres per kernel batch (0 = default)")
+    p.add_argument("--cluster-size", type=int, default=0, help="engine knob: centres per union-Gram cluster (0 = default)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     return p.parse_args()
@@ -260,6 +262,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     eng = sl.get_engine(local)
+    if args.batch_centres or args.cluster_size:
+        eng.configure(cluster_size=args.cluster_size, batch_centres=args.batch_centres)
     stream = torch.cuda.ExternalStream(eng.stream_ptr, device=device)
     K, W, cps, k = args.steps, args.warmup, args.centres_per_step, args.n_neighbors
 

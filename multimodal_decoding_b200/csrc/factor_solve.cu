@@ -209,42 +209,69 @@ __device__ __forceinline__ void split_times_tri(Frag<2>& acc, const double* __re
 }
 
 // Negated initial value of NBW column blocks of a strip of the current panel, starting at column col0:
-// -(G[loc, loc] + alpha I) for rows of A, -E for the evaluation rows.
+// -(G[loc, loc] + alpha I) for rows of A, -E for the evaluation rows.  Two passes: every load is issued
+// first (unconditionally, padding indices clamped to a valid address), the fix-ups follow, so the gather
+// costs one memory round trip instead of one per element.
 template <int NBW>
 __device__ __forceinline__ void strip_init(Frag<NBW>& acc, const CentreTask& task, const SolveParams& prm, bool is_eval,
                                            int row0, int col0, int lane) {
     const int fr = lane >> 2, fk = lane & 3;
     const int k = prm.k;
-    int lj[NBW][2], vj[NBW][2];
+    int lj[NBW][2];
 #pragma unroll
     for (int nb = 0; nb < NBW; ++nb)
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
             const int c = col0 + nb * 8 + 2 * fk + q;
             lj[nb][q] = c < k ? __ldg((is_eval ? task.nbr : task.loc) + c) : -1;
-            vj[nb][q] = c;
+        }
+    if (is_eval) {
+        const unsigned short* xe = reinterpret_cast<const unsigned short*>(prm.Xe);
+        unsigned short raw[2][NBW][2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int nb = 0; nb < NBW; ++nb)
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const int l = lj[nb][q];
+                    raw[i][nb][q] = __ldg(xe + (long)(l >= 0 ? l : 0) * EVAL_PAD + row0 + 8 * i + fr);
+                }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int nb = 0; nb < NBW; ++nb)
+#pragma unroll
+                for (int q = 0; q < 2; ++q)
+                    acc.v[i][nb][q] = lj[nb][q] >= 0 ? -h2d(__ushort_as_half(raw[i][nb][q])) : 0.0;
+    } else {
+        int li[2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int r = row0 + 8 * i + fr;
+            li[i] = r < k ? __ldg(task.loc + r) : -1;
         }
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const int r = row0 + 8 * i + fr;                 // row of A, or evaluation trial index
-        const int li = is_eval ? 0 : (r < k ? __ldg(task.loc + r) : -1);
+        for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int nb = 0; nb < NBW; ++nb)
+            for (int nb = 0; nb < NBW; ++nb)
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                const int l = lj[nb][q];
-                double v;
-                if (is_eval) {
-                    v = l >= 0 ? h2d(prm.Xe[(long)l * EVAL_PAD + r]) : 0.0;
-                } else if (li >= 0 && l >= 0) {
-                    const int hi = li > l ? li : l, lo = li > l ? l : li;
-                    v = task.gram[(long)hi * task.gram_ld + lo];
-                    if (r == vj[nb][q]) v += prm.alpha;
-                } else {
-                    v = (r == vj[nb][q]) ? 1.0 : 0.0;    // padding rows/columns: identity
+                for (int q = 0; q < 2; ++q) {
+                    const int a = li[i] >= 0 ? li[i] : 0, b = lj[nb][q] >= 0 ? lj[nb][q] : 0;
+                    const int hi = a > b ? a : b, lo = a > b ? b : a;
+                    acc.v[i][nb][q] = __ldg(task.gram + (long)hi * task.gram_ld + lo);
                 }
-                acc.v[i][nb][q] = -v;
-            }
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int nb = 0; nb < NBW; ++nb)
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const bool diag = row0 + 8 * i + fr == col0 + nb * 8 + 2 * fk + q;
+                    const bool real = li[i] >= 0 && lj[nb][q] >= 0;
+                    const double v = real ? acc.v[i][nb][q] + (diag ? prm.alpha : 0.0) : (diag ? 1.0 : 0.0);   // padding: identity
+                    acc.v[i][nb][q] = -v;
+                }
     }
 }
 
