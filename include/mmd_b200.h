@@ -30,8 +30,8 @@ typedef struct mmd_handle mmd_handle;
 #define MMD_N_SCORES 8          /* order: see MMD_SCORE_NAMES in mmd_score_name() */
 #define MMD_EVAL_PAD 144        /* test + imagery trials per centre must be <= 143 */
 
-/* Number of stage timers reported by mmd_get_stats (pack, xty, prep, syrk, factor_solve, predict, score, knn). */
-#define MMD_N_STAGES 8
+/* Number of stage timers reported by mmd_get_stats (pack, xty, prep, syrk, factor_solve, predict, score, knn, null). */
+#define MMD_N_STAGES 9
 
 int mmd_create(int device, mmd_handle** out);
 void mmd_destroy(mmd_handle* h);
@@ -73,6 +73,30 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
  *   flags_out    (n_centres) int32, 1 where the normal matrix was not positive definite; may be NULL */
 int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
                     double* scores_out, int32_t* flags_out);
+
+/* mmd_searchlight plus the null-distribution branch of train_and_test (searchlight.py:61-79): for each of
+ * `n_perm` target permutations the fixed predictions are re-scored against permuted targets.
+ *   perm_test     (n_perm x n_test) int32: entry [p][g] is the test trial (position in test_ids order) whose latent
+ *                 takes the place of trial g's latent, i.e. `indices` of y_test[indices] (data.py:540-561)
+ *   perm_imagery  (n_perm x n_imagery) int32: the same for the imagery latents (the reference draws one of the two
+ *                 3-derangements per permutation, searchlight.py:65)
+ *   null_out      (n_centres x n_perm x 6) float64, HOST or DEVICE; per permutation: captions, images, imagery,
+ *                 imagery_whole_test_set, imagery_no_std, imagery_whole_test_set_no_std (the reference's dict order) */
+#define MMD_N_NULL_SCORES 6
+int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
+                         const int32_t* perm_test, const int32_t* perm_imagery, int n_perm, double* scores_out,
+                         int32_t* flags_out, double* null_out);
+
+/* eval.py primitives for arbitrary shapes, HOST float64 row-major buffers.
+ *   mmd_cosine_distances          get_distance_matrix(predictions, originals, "cosine")   eval.py:103-104
+ *   mmd_dist_mat_to_pairwise_acc  dist_mat_to_pairwise_acc(dist_mat)                      eval.py:107-113
+ *   mmd_pairwise_accuracy         pairwise_accuracy(latents, predictions, "cosine",
+ *                                 standardize_predictions, standardize_latents)          eval.py:116-123 */
+int mmd_cosine_distances(mmd_handle* h, const double* predictions, int n_pred, const double* originals, int n_orig,
+                         int n_dims, double* dist_out);
+int mmd_dist_mat_to_pairwise_acc(mmd_handle* h, const double* dist_mat, int n_rows, int n_cols, double* acc_out);
+int mmd_pairwise_accuracy(mmd_handle* h, const double* latents, int n_lat, const double* predictions, int n_pred,
+                          int n_dims, int standardize_predictions, int standardize_latents, double* acc_out);
 
 /* Test/diagnostic hook: predictions of one centre, (143 x n_dims) float64 in the internal row order
  * [caption test trials, image test trials, imagery trials]; HOST pointer. */

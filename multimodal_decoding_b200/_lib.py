@@ -6,12 +6,14 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmmd_b200.so")
 
 N_SCORES = 8
-N_STAGES = 8
+N_STAGES = 9
+N_NULL_SCORES = 6
 EVAL_PAD = 144
 
 EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_upload",
     "mmd_searchlight", "mmd_predict_centre", "mmd_get_stats", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
+    "mmd_searchlight_null", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
 ]
 
 _lib = None
@@ -47,6 +49,14 @@ def load():
     lib.mmd_upload.restype = i32
     lib.mmd_searchlight.argtypes = [vp, vp, i32, i32, dbl, vp, vp]
     lib.mmd_searchlight.restype = i32
+    lib.mmd_searchlight_null.argtypes = [vp, vp, i32, i32, dbl, vp, vp, i32, vp, vp, vp]
+    lib.mmd_searchlight_null.restype = i32
+    lib.mmd_cosine_distances.argtypes = [vp, vp, i32, vp, i32, i32, vp]
+    lib.mmd_cosine_distances.restype = i32
+    lib.mmd_dist_mat_to_pairwise_acc.argtypes = [vp, vp, i32, i32, C.POINTER(dbl)]
+    lib.mmd_dist_mat_to_pairwise_acc.restype = i32
+    lib.mmd_pairwise_accuracy.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, C.POINTER(dbl)]
+    lib.mmd_pairwise_accuracy.restype = i32
     lib.mmd_predict_centre.argtypes = [vp, vp, i32, dbl, vp]
     lib.mmd_predict_centre.restype = i32
     lib.mmd_get_stats.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i64), C.POINTER(i64), C.POINTER(dbl)]

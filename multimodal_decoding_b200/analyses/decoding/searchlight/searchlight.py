@@ -106,14 +106,26 @@ def train_and_test(estimator, X, y=None, *, train_ids, test_ids, imagery_ids, nu
     return res[0]
 
 
+def _null_branch(eng, A, list_indices, alpha, n_imagery, null_distr_dir, shuffled_indices):
+    """Scores + the reference's per-centre null pickles (searchlight.py:61-79) for the centres in `A`."""
+    from .null_distribution import null_scores, write_null_distribution
+    if shuffled_indices is None:
+        raise ValueError("null_distr_dir is set but shuffled_indices is None (searchlight.py:63 iterates over it)")
+    scores, flags, null = null_scores(eng, A, alpha, shuffled_indices, n_imagery=n_imagery)
+    write_null_distribution(null, list_indices, null_distr_dir)
+    return scores, flags
+
+
 def custom_group_iter_search_light(list_rows, list_indices, estimator, X, y, train_ids, test_ids, imagery_ids,
                                    thread_id, null_distr_dir=None, shuffled_indices=None):
     """A chunk of centres; returns a list of score dicts (searchlight.py:93-114)."""
-    if null_distr_dir is not None:
-        from .null_distribution import write_null_distribution
-        write_null_distribution(list_rows, list_indices, estimator, X, y, train_ids, test_ids, imagery_ids,
-                                null_distr_dir, shuffled_indices)
-    scores, _ = search_light_scores(X, y, estimator, list_rows, train_ids, test_ids, imagery_ids)
+    if null_distr_dir is None:
+        scores, _ = search_light_scores(X, y, estimator, list_rows, train_ids, test_ids, imagery_ids)
+    else:
+        eng = get_engine()
+        eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
+        scores, _ = _null_branch(eng, _rectangular(list_rows), list_indices, _estimator_alpha(estimator),
+                                 len(imagery_ids), null_distr_dir, shuffled_indices)
     return list(_scores_to_dicts(scores))
 
 
@@ -130,11 +142,13 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
     A = _rectangular(A)
     local_only = n_jobs == 1
     lo, hi = (0, len(A)) if local_only else shard_range(len(A))
-    if null_distr_dir is not None:
-        from .null_distribution import write_null_distribution
-        write_null_distribution(A[lo:hi], np.arange(lo, hi), estimator, X, y, train_ids, test_ids, imagery_ids,
-                                null_distr_dir, shuffled_indices)
-    scores, flags = search_light_scores(X, y, estimator, A[lo:hi], train_ids, test_ids, imagery_ids)
+    if null_distr_dir is None:
+        scores, flags = search_light_scores(X, y, estimator, A[lo:hi], train_ids, test_ids, imagery_ids)
+    else:
+        eng = get_engine()
+        eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
+        scores, flags = _null_branch(eng, A[lo:hi], np.arange(lo, hi), _estimator_alpha(estimator), len(imagery_ids),
+                                     null_distr_dir, shuffled_indices)
     if verbose:
         print(f"searchlight: centres {lo}..{hi} done on device {get_engine().device}, "
               f"{int(flags.sum())} not positive definite")

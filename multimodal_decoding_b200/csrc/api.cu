@@ -22,8 +22,8 @@ using namespace mmd;
 
 namespace {
 
-enum Stage { ST_PACK = 0, ST_XTY, ST_PREP, ST_SYRK, ST_SOLVE, ST_PREDICT, ST_SCORE, ST_KNN };
-const char* kStageNames[MMD_N_STAGES] = {"pack", "xty", "prep", "syrk", "factor_solve", "predict", "score", "knn"};
+enum Stage { ST_PACK = 0, ST_XTY, ST_PREP, ST_SYRK, ST_SOLVE, ST_PREDICT, ST_SCORE, ST_KNN, ST_NULL };
+const char* kStageNames[MMD_N_STAGES] = {"pack", "xty", "prep", "syrk", "factor_solve", "predict", "score", "knn", "null"};
 const char* kScoreNames[MMD_N_SCORES] = {
     "pairwise_acc_captions",
     "pairwise_acc_images",
@@ -74,6 +74,10 @@ struct mmd_handle {
     // per-call / per-batch workspaces
     DevBuf adj, union_vertices, task_row, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
+    // null-distribution scoring (optional) and the generic eval.py primitives
+    DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
+    int n_perm = 0;
+    std::vector<int> int_of_test;   // position in test_ids order -> internal evaluation row (captions first)
     // knobs
     int cluster_size = 128, batch_centres = 2048, host_threads = 0;
     // stats
@@ -251,7 +255,7 @@ int run_xty(mmd_handle* h) {
 }
 
 // One batch = clusters [c0, c1).  `slot0` = first output slot when yhat_only (diagnostic) is set.
-int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, double alpha) {
+int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, double alpha, bool with_null) {
     const int n_cl = c1 - c0;
     const int t0 = plan.cl_off[c0], n_tasks = plan.cl_off[c1] - t0;
     std::vector<int> task_row(n_tasks), task_un_n(n_tasks);
@@ -346,13 +350,30 @@ int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, do
     sc.n_img = h->n_img;
     sc.n_im = h->n_im;
     sc.scores = h->scores.as<double>();
+    sc.dist_out = with_null ? h->dist.as<double>() : nullptr;
     span_begin(h, ST_SCORE);
     CU(launch_score(sc, h->stream));
     span_end(h);
+    if (with_null) {
+        NullParams np{};
+        np.tasks = sp.tasks;
+        np.n_tasks = n_tasks;
+        np.dist = h->dist.as<double>();
+        np.perm_test = h->perm_test.as<int>();
+        np.perm_imagery = h->perm_im.as<int>();
+        np.n_perm = h->n_perm;
+        np.n_cap = h->n_cap;
+        np.n_img = h->n_img;
+        np.n_im = h->n_im;
+        np.null_out = h->null_out.as<double>();
+        span_begin(h, ST_NULL);
+        CU(launch_null_score(np, h->stream));
+        span_end(h);
+    }
     return 0;
 }
 
-int run_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha) {
+int run_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha, bool with_null = false) {
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight");
     if (k < 1 || k > h->V) return fail(h, "k=%d out of range (1..%d)", k, h->V);
     if (k > h->n_train)
@@ -400,9 +421,13 @@ int run_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int 
     CU(h->misc_flag.ensure(sizeof(int)));
     CU(cudaMemsetAsync(h->misc_flag.p, 0, sizeof(int), h->stream));
     CU(cudaMemsetAsync(h->flags.p, 0, (size_t)n_centres * sizeof(int), h->stream));
+    if (with_null) {
+        CU(h->dist.ensure((size_t)max_tasks * NULL_DIST_ROWS * EVAL_PAD * sizeof(double)));
+        CU(h->null_out.ensure((size_t)n_centres * h->n_perm * 6 * sizeof(double)));
+    }
 
     for (size_t b = 0; b + 1 < batch_start.size(); ++b)
-        if (run_batch(h, plan, batch_start[b], batch_start[b + 1], k, kp, alpha)) return 1;
+        if (run_batch(h, plan, batch_start[b], batch_start[b + 1], k, kp, alpha, with_null)) return 1;
     return 0;
 }
 
@@ -439,7 +464,9 @@ void mmd_destroy(mmd_handle* h) {
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
                       &h->task_row, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
-                      &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp};
+                      &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
+                      &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
+                      &h->pa_sq, &h->pa_count};
     for (DevBuf* b : bufs) b->release();
     for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream);
@@ -555,10 +582,11 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
     // evaluation rows in the internal order: captions, images, imagery
     std::vector<int> eval_ids;
     h->n_cap = 0;
+    h->int_of_test.assign(n_test, 0);
     for (int i = 0; i < n_test; ++i)
-        if (test_is_caption[i]) { eval_ids.push_back(test_ids[i]); ++h->n_cap; }
+        if (test_is_caption[i]) { h->int_of_test[i] = (int)eval_ids.size(); eval_ids.push_back(test_ids[i]); ++h->n_cap; }
     for (int i = 0; i < n_test; ++i)
-        if (!test_is_caption[i]) eval_ids.push_back(test_ids[i]);
+        if (!test_is_caption[i]) { h->int_of_test[i] = (int)eval_ids.size(); eval_ids.push_back(test_ids[i]); }
     h->n_img = n_test - h->n_cap;
     for (int i = 0; i < n_imagery; ++i) eval_ids.push_back(imagery_ids[i]);
     const int n_eval = (int)eval_ids.size();
@@ -663,6 +691,115 @@ int mmd_predict_centre(mmd_handle* h, const int32_t* neighbours, int k, double a
                          (size_t)h->D * sizeof(double), n_eval, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
+    return 0;
+}
+
+int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
+                         const int32_t* perm_test, const int32_t* perm_imagery, int n_perm, double* scores_out,
+                         int32_t* flags_out, double* null_out) {
+    if (!h) return 1;
+    if (!adjacency || !scores_out || !perm_test || !null_out || (h->n_im > 0 && !perm_imagery))
+        return fail(h, "mmd_searchlight_null: null pointer");
+    if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight_null");
+    if (n_centres < 0 || n_perm < 1 || n_perm > 8192) return fail(h, "mmd_searchlight_null: bad n_centres / n_perm");
+    if (n_centres == 0) return 0;
+    const int n_test = h->n_test;
+    for (long i = 0; i < (long)n_perm * n_test; ++i)
+        if (perm_test[i] < 0 || perm_test[i] >= n_test) return fail(h, "mmd_searchlight_null: test permutation index out of range");
+    for (long i = 0; i < (long)n_perm * h->n_im; ++i)
+        if (perm_imagery[i] < 0 || perm_imagery[i] >= h->n_im) return fail(h, "mmd_searchlight_null: imagery permutation index out of range");
+    CU(cudaSetDevice(h->device));
+    h->n_perm = n_perm;
+    {   // test-order positions -> internal evaluation rows, for rows and values alike
+        std::vector<int> internal((size_t)n_perm * n_test);
+        for (int p = 0; p < n_perm; ++p)
+            for (int pos = 0; pos < n_test; ++pos)
+                internal[(size_t)p * n_test + h->int_of_test[pos]] = h->int_of_test[perm_test[(size_t)p * n_test + pos]];
+        if (to_device(h, h->perm_test, internal.data(), internal.size())) return 1;
+        CU(cudaStreamSynchronize(h->stream));          // `internal` is pageable and goes out of scope
+    }
+    if (to_device(h, h->perm_im, perm_imagery, (size_t)n_perm * h->n_im)) return 1;
+    if (run_searchlight(h, adjacency, n_centres, k, alpha, true)) {
+        cudaStreamSynchronize(h->stream);
+        h->spans.clear();
+        h->events_used = 0;
+        return 1;
+    }
+    int bad = 0;
+    CU(cudaMemcpyAsync(&bad, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(scores_out, h->scores.p, (size_t)n_centres * MMD_N_SCORES * sizeof(double), cudaMemcpyDefault, h->stream));
+    CU(cudaMemcpyAsync(null_out, h->null_out.p, (size_t)n_centres * n_perm * 6 * sizeof(double), cudaMemcpyDefault, h->stream));
+    if (flags_out) CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    resolve_spans(h);
+    if (bad == 2) return fail(h, "mmd_searchlight_null: adjacency holds a vertex index outside [0, %d)", h->V);
+    if (bad == 1) return fail(h, "internal: neighbour missing from its cluster union");
+    return 0;
+}
+
+// ---- eval.py primitives on arbitrary shapes (host float64 buffers) ----
+static int stage_eval_inputs(mmd_handle* h, const double* predictions, int n_pred, const double* latents, int n_lat,
+                             int n_dims, int std_pred, int std_lat) {
+    if (to_device(h, h->pa_pred, predictions, (size_t)n_pred * n_dims)) return 1;
+    if (to_device(h, h->pa_lat, latents, (size_t)n_lat * n_dims)) return 1;
+    CU(h->pa_dist.ensure((size_t)n_pred * n_lat * sizeof(double)));
+    CU(h->pa_sq.ensure((size_t)(n_pred + n_lat) * sizeof(double)));
+    CU(h->pa_count.ensure(sizeof(unsigned long long)));
+    if (std_pred) CU(launch_standardize_columns(h->pa_pred.as<double>(), n_pred, n_dims, n_dims, h->stream));
+    if (std_lat) CU(launch_standardize_columns(h->pa_lat.as<double>(), n_lat, n_dims, n_dims, h->stream));
+    CU(launch_cosine_dist(h->pa_pred.as<double>(), n_pred, h->pa_lat.as<double>(), n_lat, n_dims, n_dims,
+                          h->pa_sq.as<double>(), h->pa_sq.as<double>() + n_pred, h->pa_dist.as<double>(), h->stream));
+    h->launches += 3 + (std_pred ? 1 : 0) + (std_lat ? 1 : 0);
+    return 0;
+}
+
+int mmd_cosine_distances(mmd_handle* h, const double* predictions, int n_pred, const double* originals, int n_orig,
+                         int n_dims, double* dist_out) {
+    if (!h) return 1;
+    if (!predictions || !originals || !dist_out) return fail(h, "mmd_cosine_distances: null pointer");
+    if (n_pred < 1 || n_orig < 1 || n_dims < 1) return fail(h, "mmd_cosine_distances: empty input");
+    CU(cudaSetDevice(h->device));
+    if (stage_eval_inputs(h, predictions, n_pred, originals, n_orig, n_dims, 0, 0)) return 1;
+    CU(cudaMemcpyAsync(dist_out, h->pa_dist.p, (size_t)n_pred * n_orig * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int mmd_pairwise_accuracy(mmd_handle* h, const double* latents, int n_lat, const double* predictions, int n_pred,
+                          int n_dims, int standardize_predictions, int standardize_latents, double* acc_out) {
+    if (!h) return 1;
+    if (!latents || !predictions || !acc_out) return fail(h, "mmd_pairwise_accuracy: null pointer");
+    if (n_pred < 1 || n_lat < 1 || n_dims < 1) return fail(h, "mmd_pairwise_accuracy: empty input");
+    if (n_pred > n_lat && n_lat != 1)
+        return fail(h, "mmd_pairwise_accuracy: %d predictions but %d candidate latents: the diagonal (eval.py:108) "
+                       "cannot be broadcast against the distance matrix", n_pred, n_lat);
+    CU(cudaSetDevice(h->device));
+    if (stage_eval_inputs(h, predictions, n_pred, latents, n_lat, n_dims, standardize_predictions, standardize_latents)) return 1;
+    CU(launch_pairwise_count(h->pa_dist.as<double>(), n_pred, n_lat, h->pa_count.as<unsigned long long>(), h->stream));
+    h->launches += 1;
+    unsigned long long count = 0;
+    CU(cudaMemcpyAsync(&count, h->pa_count.p, sizeof(count), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    const long rows = n_pred < n_lat ? n_pred : n_lat;
+    *acc_out = (double)count / (double)((long)n_pred * n_lat - rows);
+    return 0;
+}
+
+int mmd_dist_mat_to_pairwise_acc(mmd_handle* h, const double* dist_mat, int n_rows, int n_cols, double* acc_out) {
+    if (!h) return 1;
+    if (!dist_mat || !acc_out) return fail(h, "mmd_dist_mat_to_pairwise_acc: null pointer");
+    if (n_rows < 1 || n_cols < 1) return fail(h, "mmd_dist_mat_to_pairwise_acc: empty matrix");
+    if (n_rows > n_cols && n_cols != 1) return fail(h, "mmd_dist_mat_to_pairwise_acc: more rows than columns (eval.py:108-109 cannot broadcast)");
+    CU(cudaSetDevice(h->device));
+    if (to_device(h, h->pa_dist, dist_mat, (size_t)n_rows * n_cols)) return 1;
+    CU(h->pa_count.ensure(sizeof(unsigned long long)));
+    CU(launch_pairwise_count(h->pa_dist.as<double>(), n_rows, n_cols, h->pa_count.as<unsigned long long>(), h->stream));
+    h->launches += 1;
+    unsigned long long count = 0;
+    CU(cudaMemcpyAsync(&count, h->pa_count.p, sizeof(count), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    const long rows = n_rows < n_cols ? n_rows : n_cols;
+    *acc_out = (double)count / (double)((long)n_rows * n_cols - rows);
     return 0;
 }
 

@@ -75,9 +75,30 @@ struct ScoreParams {
     const double* cand_sq;     // squared norms of the candidate rows
     int n_cap, n_img, n_im;
     double* scores;            // (n_centres x 8), written at row task.centre
+    double* dist_out;          // optional: per task NULL_DIST_ROWS x EVAL_PAD cosine distances (null-distribution input)
 };
+// rows 0..n_eval-1: standardised predictions (captions, images, imagery); rows EVAL_PAD..: raw imagery predictions
+constexpr int NULL_DIST_ROWS = 160;
 size_t score_smem_bytes(int Dp);
 cudaError_t launch_score(const ScoreParams& p, cudaStream_t s);
+
+// ---- null_score.cu ----------------------------------------------------------------------
+struct NullParams {
+    const CentreTask* tasks;
+    int n_tasks;
+    const double* dist;        // as written by the score kernel
+    const int* perm_test;      // (n_perm x n_test) candidate column playing the role of test row g's own latent
+    const int* perm_imagery;   // (n_perm x n_im)   imagery candidate (0..n_im-1) playing the role of imagery row i's latent
+    int n_perm, n_cap, n_img, n_im;
+    double* null_out;          // (n_centres x n_perm x 6), written at row task.centre
+};
+cudaError_t launch_null_score(const NullParams& p, cudaStream_t s);
+
+// ---- pairwise.cu ------------------------------------------------------------------------
+cudaError_t launch_standardize_columns(double* A, int n, int D, long ld, cudaStream_t s);
+cudaError_t launch_cosine_dist(const double* P, int np, const double* C, int nc, int D, long ld, double* psq, double* csq,
+                               double* dist, cudaStream_t s);
+cudaError_t launch_pairwise_count(const double* dist, int r, int c, unsigned long long* count, cudaStream_t s);
 
 // ---- prep.cu -----------------------------------------------------------------------------
 cudaError_t launch_prep_tasks(const int* adjacency, int k, int kp, const int* task_row, const long* task_union_off,

@@ -179,6 +179,8 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
                     const int n = warp * 16 + j * 8 + 2 * fk + e;
                     const double dv = 1.0 - acc[i][j][e] / (rn * sqrt(prm.cand_sq[n]));
                     acc[i][j][e] = dv;
+                    if (prm.dist_out && gm < NULL_DIST_ROWS)
+                        prm.dist_out[((long)task_id * NULL_DIST_ROWS + gm) * EVAL_PAD + n] = dv;
                     if (gm < n_test) {
                         if (n == gm) dsame_sm[gm] = dv;
                         const int li = gm < n_cap ? gm : gm - n_cap;

@@ -117,6 +117,59 @@ class Engine:
                                               flags.ctypes.data))
         return scores, flags
 
+    def searchlight_null(self, adjacency, alpha, perm_test, perm_imagery):
+        """Scores plus the null-distribution scores (searchlight.py:61-79) for target permutations given as index
+        arrays into the test / imagery trials; returns (scores (n,8), flags (n,), null (n, n_perm, 6))."""
+        adj = np.ascontiguousarray(np.asarray(adjacency, dtype=np.int32))
+        if adj.ndim != 2:
+            raise ValueError("adjacency must be rectangular (n_centres, k); ragged radius mode is not supported")
+        pt = np.ascontiguousarray(np.asarray(perm_test, dtype=np.int32))
+        pi = np.ascontiguousarray(np.asarray(perm_imagery, dtype=np.int32))
+        if pt.ndim != 2 or pi.ndim != 2 or len(pt) != len(pi):
+            raise ValueError("perm_test (n_perm, n_test) and perm_imagery (n_perm, n_imagery) must have one row per permutation")
+        n, k = adj.shape
+        n_perm = len(pt)
+        scores = np.empty((n, _lib.N_SCORES), dtype=np.float64)
+        flags = np.zeros(n, dtype=np.int32)
+        null = np.empty((n, n_perm, _lib.N_NULL_SCORES), dtype=np.float64)
+        self._check(self._lib.mmd_searchlight_null(self._h, adj.ctypes.data, n, k, float(alpha), pt.ctypes.data,
+                                                   pi.ctypes.data, n_perm, scores.ctypes.data, flags.ctypes.data,
+                                                   null.ctypes.data))
+        return scores, flags, null
+
+    # -- eval.py primitives (arbitrary shapes, float64) -----------------------------------------
+    @staticmethod
+    def _f64(a, name):
+        a = np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+        if a.ndim != 2:
+            raise ValueError(f"{name} must be 2-D (rows x features)")
+        return a
+
+    def cosine_distances(self, predictions, originals):
+        p, o = self._f64(predictions, "predictions"), self._f64(originals, "originals")
+        if p.shape[1] != o.shape[1]:
+            raise ValueError(f"XA and XB must have the same number of columns ({p.shape[1]} != {o.shape[1]})")
+        out = np.empty((len(p), len(o)), dtype=np.float64)
+        self._check(self._lib.mmd_cosine_distances(self._h, p.ctypes.data, len(p), o.ctypes.data, len(o), p.shape[1],
+                                                   out.ctypes.data))
+        return out
+
+    def dist_mat_to_pairwise_acc(self, dist_mat):
+        d = self._f64(dist_mat, "dist_mat")
+        acc = C.c_double()
+        self._check(self._lib.mmd_dist_mat_to_pairwise_acc(self._h, d.ctypes.data, d.shape[0], d.shape[1], C.byref(acc)))
+        return acc.value
+
+    def pairwise_accuracy(self, latents, predictions, standardize_predictions=False, standardize_latents=False):
+        lat, pred = self._f64(latents, "latents"), self._f64(predictions, "predictions")
+        if lat.shape[1] != pred.shape[1]:
+            raise ValueError(f"XA and XB must have the same number of columns ({pred.shape[1]} != {lat.shape[1]})")
+        acc = C.c_double()
+        self._check(self._lib.mmd_pairwise_accuracy(self._h, lat.ctypes.data, len(lat), pred.ctypes.data, len(pred),
+                                                    lat.shape[1], int(bool(standardize_predictions)),
+                                                    int(bool(standardize_latents)), C.byref(acc)))
+        return acc.value
+
     def predict_centre(self, neighbours, alpha: float = 1.0):
         nb = np.ascontiguousarray(np.asarray(neighbours, dtype=np.int32))
         out = np.empty((self.n_eval, self.n_dims), dtype=np.float64)

@@ -67,7 +67,7 @@ def gather_scores(local_scores: np.ndarray, n_total: int) -> np.ndarray:
     dev = torch.device("cuda", torch.cuda.current_device()) if on_gpu else torch.device("cpu")
     mine = torch.zeros((longest, width), dtype=torch.float64, device=dev)
     mine[: len(local_scores)] = torch.from_numpy(np.ascontiguousarray(local_scores)).to(dev)
-    everyone = torch.empty((world, longest, width), dtype=torch.float64, device=dev)
+    everyone = torch.empty((world * longest, width), dtype=torch.float64, device=dev)   # flat: accepted by NCCL and gloo
     dist.all_gather_into_tensor(everyone, mine)
-    everyone = everyone.cpu().numpy()
+    everyone = everyone.cpu().numpy().reshape(world, longest, width)
     return np.concatenate([everyone[r, : hi - lo] for r, (lo, hi) in enumerate(bounds)])
