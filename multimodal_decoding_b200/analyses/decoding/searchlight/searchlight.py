@@ -11,14 +11,26 @@ reference's vertex order.
 """
 from __future__ import annotations
 
+import argparse
+import gc
 import os
 import pickle
+import time
 
 import numpy as np
 
+from ....data import (TEST_STIM_TYPES, get_fmri_surface_data, SELECT_DEFAULT, LatentFeatsConfig,
+                      create_null_distr_shuffled_indices, standardize_fmri_betas, standardize_latents,
+                      get_latent_features, SPLIT_TRAIN, MODALITY_AGNOSTIC, SPLIT_TEST, SPLIT_IMAGERY, TRAINING_MODES,
+                      FEATURE_COMBINATION_CHOICES, VISION_FEAT_COMBINATION_CHOICES, LANG_FEAT_COMBINATION_CHOICES,
+                      get_data_provider, _CURRENT_MODEL)
 from ....engine import Engine, score_keys
+from ....eval import ACC_CAPTIONS, ACC_IMAGES, ACC_IMAGERY, ACC_IMAGERY_WHOLE_TEST
+from ....utils import SUBJECTS, DATA_DIR, DEFAULT_RESOLUTION, FMRI_BETAS_SURFACE_DIR, DEFAULT_MODEL
 
 DEFAULT_N_JOBS = 10                                   # searchlight.py:30 (kept for CLI compatibility)
+SEARCHLIGHT_OUT_DIR = os.path.join(DATA_DIR, "searchlight")                                     # searchlight.py:32
+SEARCHLIGHT_PERMUTATION_TESTING_RESULTS_DIR = os.path.join(SEARCHLIGHT_OUT_DIR, "permutation_testing_results")
 DERANGEMENTS_THREE_DIMS = [[1, 2, 0], [2, 0, 1]]      # searchlight.py:35
 
 _ENGINES: dict[int, Engine] = {}
@@ -153,3 +165,176 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
         print(f"searchlight: centres {lo}..{hi} done on device {get_engine().device}, "
               f"{int(flags.sum())} not positive definite")
     return _scores_to_dicts(scores if local_only else gather_scores(scores, len(A)))
+
+
+def get_adjacency_matrix(hemi, resolution, nan_locations=None, radius=None, num_neighbors=None):
+    """searchlight.py:152-178.  k-NN branch: exact float64 k-NN on the GPU (`mmd_knn`), bit-identical to sklearn's
+    `NearestNeighbors().kneighbors` on tie-free coordinates.  The mesh comes from the data provider (the reference
+    loads nilearn's inflated fsaverage surface; nilearn is not on this box)."""
+    coords = np.asarray(get_data_provider().mesh(hemi, resolution).coords)
+    if nan_locations is not None:
+        coords = coords[~nan_locations]
+    nearest_neighbors = None
+    distances = None
+    if radius is not None:
+        raise NotImplementedError("radius-mode (ragged) neighbourhoods, searchlight.py:164-171, are not built yet "
+                                  "(SURVEY.md §8f #4); use --n-neighbors")
+    elif num_neighbors is not None:
+        eng = get_engine()
+        distances = np.empty((len(coords), num_neighbors), dtype=np.float64)
+        adjacency = np.empty((len(coords), num_neighbors), dtype=np.int64)
+        for lo in range(0, len(coords), 32768):
+            hi = min(lo + 32768, len(coords))
+            distances[lo:hi], adjacency[lo:hi] = eng.knn(coords, num_neighbors, lo, hi)
+        print(f"Max radius {num_neighbors} neighbors: {distances.max():.2f}mm")
+        print(f"Mean radius: {distances.max(axis=1).mean():.2f}mm")
+    else:
+        raise RuntimeError("Need to set either radius or n_neighbors arg!")
+    return adjacency, nearest_neighbors, distances
+
+
+def run(args):
+    """searchlight.py:181-296: same loop, prints and result pickle; data come from the installed provider."""
+    from sklearn.linear_model import Ridge
+    shuffled_indices = None
+    if args.create_null_distr:
+        shuffled_indices = create_null_distr_shuffled_indices(args.n_permutations_per_subject)
+
+    for subject in args.subjects:
+        for training_mode in args.training_modes:
+            for hemi in args.hemis:
+                feats_config = LatentFeatsConfig(
+                    args.model, args.features, args.test_features, args.vision_features, args.lang_features
+                )
+                _CURRENT_MODEL[0] = feats_config.model          # the synthetic provider sizes Y by the model
+                train_fmri, train_stim_ids, train_stim_types = get_fmri_surface_data(
+                    args.betas_dir, subject, SPLIT_TRAIN, training_mode, hemi, args.resolution
+                )
+                test_fmri, test_stim_ids, test_stim_types = get_fmri_surface_data(
+                    args.betas_dir, subject, SPLIT_TEST, hemi=hemi, resolution=args.resolution
+                )
+                imagery_fmri, imagery_stim_ids, imagery_stim_types = get_fmri_surface_data(
+                    args.betas_dir, subject, SPLIT_IMAGERY, hemi=hemi, resolution=args.resolution
+                )
+                nan_locations = np.isnan(train_fmri[0])
+                train_fmri, test_fmri, imagery_fmri = standardize_fmri_betas(train_fmri, test_fmri, imagery_fmri)
+
+                print(f"\nTRAIN MODE: {training_mode} | SUBJECT: {subject} | "
+                      f"MODEL: {feats_config.model} | FEATURES: {feats_config.features}")
+
+                train_latents = get_latent_features(feats_config, subject, SPLIT_TRAIN, training_mode)
+                test_latents = get_latent_features(feats_config, subject, SPLIT_TEST)
+                imagery_latents = get_latent_features(feats_config, subject, SPLIT_IMAGERY)
+                train_latents, test_latents, imagery_latents = standardize_latents(
+                    train_latents, test_latents, imagery_latents
+                )
+                latents = np.concatenate((train_latents, test_latents, imagery_latents))
+
+                results_dir = get_results_dir(
+                    feats_config, hemi, subject, training_mode, args.resolution, searchlight_mode_from_args(args)
+                )
+                os.makedirs(results_dir, exist_ok=True)
+
+                print("Hemisphere: ", hemi)
+                print(f"train_fmri shape: {train_fmri.shape}")
+                print(f"test_fmri shape: {test_fmri.shape}")
+                print(f"imagery_fmri shape: {imagery_fmri.shape}")
+
+                train_ids = list(range(len(train_fmri)))
+                test_ids = list(range(len(train_fmri), len(train_fmri) + len(test_fmri)))
+                imagery_ids = list(range(len(train_ids) + len(test_ids),
+                                         len(train_ids) + len(test_ids) + len(imagery_fmri)))
+
+                X = np.concatenate((train_fmri, test_fmri, imagery_fmri))
+
+                adjacency, n_neighbors, distances = get_adjacency_matrix(
+                    hemi, args.resolution, nan_locations, args.radius, args.n_neighbors
+                )
+
+                model = Ridge(alpha=args.l2_regularization_alpha, fit_intercept=False)
+
+                null_distr_dir = None
+                if args.create_null_distr:
+                    null_distr_dir = os.path.join(results_dir, "null_distr")
+                    os.makedirs(null_distr_dir, exist_ok=True)
+
+                X = X.astype(np.float16)
+                latents = latents.astype(np.float16)
+
+                start = time.time()
+                scores = custom_search_light(
+                    X, latents, estimator=model, A=adjacency, train_ids=train_ids, test_ids=test_ids,
+                    imagery_ids=imagery_ids, n_jobs=args.n_jobs, verbose=1, null_distr_dir=null_distr_dir,
+                    shuffled_indices=shuffled_indices
+                )
+                end = time.time()
+                print(f"Searchlight time: {int(end - start)}s")
+                for label, key in (("captions", ACC_CAPTIONS), ("images", ACC_IMAGES), (ACC_IMAGERY, ACC_IMAGERY),
+                                   (ACC_IMAGERY_WHOLE_TEST, ACC_IMAGERY_WHOLE_TEST)):
+                    vals = [score[key] for score in scores]
+                    print(f"Mean score ({label}): {np.mean(vals):.2f} | Max score: {np.max(vals):.2f}")
+
+                results_dict = {
+                    "nan_locations": nan_locations,
+                    "adjacency": adjacency,
+                    "n_neighbors": n_neighbors,
+                    "distances": distances,
+                    "scores": scores,
+                }
+                results_file_path = get_results_file_path(
+                    feats_config, hemi, subject, training_mode, args.resolution, searchlight_mode_from_args(args),
+                    args.l2_regularization_alpha
+                )
+                pickle.dump(results_dict, open(results_file_path, 'wb'))
+
+                del X, latents, train_fmri
+                gc.collect()
+
+
+def searchlight_mode_from_args(args):
+    if args.radius is not None:
+        return f"radius_{args.radius}"
+    elif args.n_neighbors is not None:
+        return f"n_neighbors_{args.n_neighbors}"
+    else:
+        raise RuntimeError("Need to set either radius or n_neighbors arg!")
+
+
+def get_results_dir(feats_config, hemi, subject, training_mode, resolution, mode):
+    return os.path.join(
+        SEARCHLIGHT_OUT_DIR, training_mode, feats_config.model, feats_config.combined_feats,
+        feats_config.vision_features, feats_config.lang_features, subject, resolution, hemi, mode
+    )
+
+
+def get_results_file_path(feats_config, hemi, subject, training_mode, resolution, mode, l2_regularization_alpha):
+    results_dir = get_results_dir(feats_config, hemi, subject, training_mode, resolution, mode)
+    return os.path.join(results_dir, f"alpha_{str(l2_regularization_alpha)}.p")
+
+
+def get_args(argv=None):
+    """searchlight.py:321-355: flags and defaults verbatim (argparse abbreviation keeps `--training-mode` working)."""
+    parser = argparse.ArgumentParser()
+    parser.add_argument("--betas-dir", type=str, default=FMRI_BETAS_SURFACE_DIR)
+    parser.add_argument("--training-modes", type=str, nargs="+", default=[MODALITY_AGNOSTIC], choices=TRAINING_MODES)
+    parser.add_argument("--model", type=str, default=DEFAULT_MODEL)
+    parser.add_argument("--features", type=str, default=SELECT_DEFAULT, choices=FEATURE_COMBINATION_CHOICES)
+    parser.add_argument("--test-features", type=str, default=SELECT_DEFAULT, choices=FEATURE_COMBINATION_CHOICES)
+    parser.add_argument("--vision-features", type=str, default=SELECT_DEFAULT, choices=VISION_FEAT_COMBINATION_CHOICES)
+    parser.add_argument("--lang-features", type=str, default=SELECT_DEFAULT, choices=LANG_FEAT_COMBINATION_CHOICES)
+    parser.add_argument("--subjects", type=str, nargs='+', default=SUBJECTS)
+    parser.add_argument("--resolution", type=str, default=DEFAULT_RESOLUTION)
+    parser.add_argument("--hemis", type=str, nargs="+", default=["left", "right"])
+    parser.add_argument("--l2-regularization-alpha", type=float, default=1)
+    parser.add_argument("--radius", type=float, default=None)
+    parser.add_argument("--n-neighbors", type=int, default=None)
+    parser.add_argument("--n-jobs", type=int, default=DEFAULT_N_JOBS)
+    parser.add_argument("--create-null-distr", default=False, action="store_true")
+    parser.add_argument("--n-permutations-per-subject", type=int, default=100)
+    return parser.parse_args(argv)
+
+
+if __name__ == "__main__":
+    args = get_args()
+    os.makedirs(SEARCHLIGHT_OUT_DIR, exist_ok=True)
+    run(args)
