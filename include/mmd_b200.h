@@ -54,6 +54,16 @@ const char* mmd_score_name(int i);
 int mmd_knn(mmd_handle* h, const double* coords, int n_vertices, int k, int q_begin, int q_end,
             int64_t* idx_out, double* dist_out);
 
+/* Replaces the radius branch of get_adjacency_matrix (searchlight.py:164-171, sklearn
+ * NearestNeighbors(radius=r).radius_neighbors_graph(coords) turned into one index array per vertex: ascending
+ * vertex id, the vertex itself included, squared distance <= r*r).  Two passes over queries q_begin .. q_end-1:
+ *   count pass  (indices_out == NULL): counts_out[q - q_begin] = number of neighbours
+ *   fill pass   (indices_out != NULL): offsets = exclusive prefix sum of the counts ((q_end-q_begin) + 1 entries,
+ *               offsets[0] = 0); neighbours of query q are written to indices_out[offsets[q-q_begin] ..)
+ * coords (n_vertices x 3) float64 HOST or DEVICE; offsets, counts_out, indices_out HOST. */
+int mmd_radius_neighbors(mmd_handle* h, const double* coords, int n_vertices, double radius, int q_begin, int q_end,
+                         const int64_t* offsets, int32_t* counts_out, int32_t* indices_out);
+
 /* Stages the arrays custom_search_light receives (searchlight.py:117-129; built at :217-248) on the GPU.
  *   X            (n_total x n_vertices) float16 row-major, trials x vertices
  *   Y            (n_total x n_dims)     float16 row-major, trials x embedding dims
@@ -73,6 +83,16 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
  *   flags_out    (n_centres) int32, 1 where the normal matrix was not positive definite; may be NULL */
 int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
                     double* scores_out, int32_t* flags_out);
+
+/* The same loop for ragged neighbourhoods, i.e. the radius branch of get_adjacency_matrix
+ * (searchlight.py:164-171: one index array of its own length per centre).
+ *   indices      concatenated vertex ids of all neighbourhoods, int32, HOST pointer
+ *   offsets      (n_centres + 1) int64, HOST pointer: centre i owns indices[offsets[i] .. offsets[i+1]); every
+ *                neighbourhood needs 1 .. min(2000, n_train) entries
+ *   anchors      (n_centres) int32 or NULL: the vertex each centre sits on; only used to group nearby centres so that
+ *                they share one Gram computation (NULL: the first entry of each list is used) */
+int mmd_searchlight_ragged(mmd_handle* h, const int32_t* indices, const int64_t* offsets, const int32_t* anchors,
+                           int n_centres, double alpha, double* scores_out, int32_t* flags_out);
 
 /* mmd_searchlight plus the null-distribution branch of train_and_test (searchlight.py:61-79): for each of
  * `n_perm` target permutations the fixed predictions are re-scored against permuted targets.

@@ -3,7 +3,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmmd_b200.so")
+# MMD_B200_LIB: development override used to A/B kernel variants built with build.py --variant
+LIB_PATH = os.environ.get("MMD_B200_LIB") or os.path.join(_HERE, "libmmd_b200.so")
 
 N_SCORES = 8
 N_STAGES = 9
@@ -11,8 +12,8 @@ N_NULL_SCORES = 6
 EVAL_PAD = 144
 
 EXPORTS = [
-    "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_upload",
-    "mmd_searchlight", "mmd_predict_centre", "mmd_get_stats", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
+    "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload",
+    "mmd_searchlight", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
 ]
 
@@ -45,10 +46,14 @@ def load():
     lib.mmd_stage_name.restype = C.c_char_p
     lib.mmd_knn.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp]
     lib.mmd_knn.restype = i32
+    lib.mmd_radius_neighbors.argtypes = [vp, vp, i32, dbl, i32, i32, vp, vp, vp]
+    lib.mmd_radius_neighbors.restype = i32
     lib.mmd_upload.argtypes = [vp, vp, i32, i32, vp, i32, vp, i32, vp, i32, vp, vp, i32]
     lib.mmd_upload.restype = i32
     lib.mmd_searchlight.argtypes = [vp, vp, i32, i32, dbl, vp, vp]
     lib.mmd_searchlight.restype = i32
+    lib.mmd_searchlight_ragged.argtypes = [vp, vp, vp, vp, i32, dbl, vp, vp]
+    lib.mmd_searchlight_ragged.restype = i32
     lib.mmd_searchlight_null.argtypes = [vp, vp, i32, i32, dbl, vp, vp, i32, vp, vp, vp]
     lib.mmd_searchlight_null.restype = i32
     lib.mmd_cosine_distances.argtypes = [vp, vp, i32, vp, i32, i32, vp]

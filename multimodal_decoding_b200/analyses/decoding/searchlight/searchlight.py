@@ -84,19 +84,32 @@ def _scores_to_dicts(scores: np.ndarray) -> np.ndarray:
     return out
 
 
+def _is_ragged(A):
+    return not (isinstance(A, np.ndarray) and A.dtype != object and A.ndim == 2)
+
+
 def _rectangular(A):
-    if isinstance(A, np.ndarray) and A.ndim == 2:
+    """(n, k) array for k-NN adjacency; a list of index arrays for the ragged radius-mode adjacency
+    (searchlight.py:164-166)."""
+    if isinstance(A, np.ndarray) and A.dtype != object and A.ndim == 2:
         return A
-    lens = {len(a) for a in A}
-    if len(lens) > 1:
-        raise NotImplementedError("ragged neighbourhoods (radius mode, searchlight.py:164-171) are not supported "
-                                  "by the GPU path yet; use --n-neighbors")
-    return np.asarray([np.asarray(a) for a in A]) if len(A) else np.zeros((0, 1), dtype=np.int64)
+    rows = [np.asarray(a).ravel() for a in A]
+    if len({len(r) for r in rows}) > 1:
+        return rows
+    return np.asarray(rows) if len(rows) else np.zeros((0, 1), dtype=np.int64)
+
+
+def _require_rectangular(A, what):
+    if _is_ragged(A):
+        raise NotImplementedError(f"{what} is only built for fixed-size (k-NN) neighbourhoods; "
+                                  "radius-mode neighbourhoods are scored without it")
+    return A
 
 
 def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *, device=None, is_caption=None,
-                        upload=True):
-    """(n_centres x 8) float64 score block and per-centre flags for the centres in `A` on one GPU."""
+                        upload=True, anchors=None):
+    """(n_centres x 8) float64 score block and per-centre flags for the centres in `A` on one GPU.
+    `anchors` (ragged `A` only): the vertex each centre sits on, used to group nearby centres."""
     eng = get_engine(device)
     alpha = _estimator_alpha(estimator)
     A = _rectangular(A)
@@ -104,6 +117,8 @@ def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *,
         if is_caption is None:
             is_caption = _is_caption_mask(len(test_ids))
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption)
+    if _is_ragged(A):
+        return eng.searchlight_ragged(A, alpha, anchors)
     return eng.searchlight(A, alpha)
 
 
@@ -136,7 +151,8 @@ def custom_group_iter_search_light(list_rows, list_indices, estimator, X, y, tra
     else:
         eng = get_engine()
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
-        scores, _ = _null_branch(eng, _rectangular(list_rows), list_indices, _estimator_alpha(estimator),
+        scores, _ = _null_branch(eng, _require_rectangular(_rectangular(list_rows), "the null-distribution branch"),
+                                 list_indices, _estimator_alpha(estimator),
                                  len(imagery_ids), null_distr_dir, shuffled_indices)
     return list(_scores_to_dicts(scores))
 
@@ -155,8 +171,12 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
     local_only = n_jobs == 1
     lo, hi = (0, len(A)) if local_only else shard_range(len(A))
     if null_distr_dir is None:
-        scores, flags = search_light_scores(X, y, estimator, A[lo:hi], train_ids, test_ids, imagery_ids)
+        # radius mode: centre i sits on vertex i (searchlight.py:143-148 enumerates the rows of A by vertex)
+        anchors = np.arange(lo, hi) if _is_ragged(A) and len(A) == np.shape(X)[1] else None
+        scores, flags = search_light_scores(X, y, estimator, A[lo:hi], train_ids, test_ids, imagery_ids,
+                                            anchors=anchors)
     else:
+        _require_rectangular(A, "the null-distribution branch")
         eng = get_engine()
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
         scores, flags = _null_branch(eng, A[lo:hi], np.arange(lo, hi), _estimator_alpha(estimator), len(imagery_ids),
@@ -177,8 +197,13 @@ def get_adjacency_matrix(hemi, resolution, nan_locations=None, radius=None, num_
     nearest_neighbors = None
     distances = None
     if radius is not None:
-        raise NotImplementedError("radius-mode (ragged) neighbourhoods, searchlight.py:164-171, are not built yet "
-                                  "(SURVEY.md §8f #4); use --n-neighbors")
+        # searchlight.py:164-171 densifies a V x V graph (`.toarray()`), which only fits low resolutions; the GPU
+        # kernel emits the same per-vertex index arrays (ascending vertex id, the vertex itself included) directly
+        adjacency = get_engine().radius_neighbors(coords, float(radius))
+        nearest_neighbors = [len(adj) for adj in adjacency]
+        print(
+            f"Number of neighbors within {radius}mm radius: {np.mean(nearest_neighbors):.1f} "
+            f"(max: {np.max(nearest_neighbors):.0f} | min: {np.min(nearest_neighbors):.0f})")
     elif num_neighbors is not None:
         eng = get_engine()
         distances = np.empty((len(coords), num_neighbors), dtype=np.float64)

@@ -19,15 +19,19 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
+def build(force=False, verbose=False, variant=None, defines=()):
+    """`variant`/`defines`: development builds of kernel variants (libmmd_b200.<variant>.so, extra -D flags),
+    loaded through the MMD_B200_LIB override of _lib.py; the product library is the default build."""
+    lib = LIB if not variant else os.path.join(HERE, f"libmmd_b200.{variant}.so")
+    if not variant and not force and not needs_build():
         return LIB
     nvcc = os.environ.get("NVCC", "nvcc")
     objs = []
     procs = []
     for src in sorted(glob.glob(os.path.join(CSRC, "*.cu"))):
-        obj = src[:-3] + ".o"
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        obj = src[:-3] + (f".{variant}.o" if variant else ".o")
+        cmd = ([nvcc] + NVCC_FLAGS + [f"-D{d}" for d in defines] + (["-Xptxas", "-v"] if verbose else [])
+               + ["-c", src, "-o", obj])
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     failed = False
@@ -38,9 +42,11 @@ def build(force=False, verbose=False):
         failed |= p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed")
-    subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-lcudart"])
-    return LIB
+    subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib] + objs + ["-lcudart"])
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    var = [a.split("=", 1)[1] for a in sys.argv if a.startswith("--variant=")]
+    defs = [a[2:] for a in sys.argv if a.startswith("-D")]
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, variant=var[0] if var else None, defines=defs))

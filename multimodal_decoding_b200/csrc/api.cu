@@ -72,7 +72,7 @@ struct mmd_handle {
     bool uploaded = false;
     DevBuf Xt, Xe, Yt, cand, cand_sq, XtY;
     // per-call / per-batch workspaces
-    DevBuf adj, union_vertices, task_row, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
+    DevBuf adj, union_vertices, task_row, task_k, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
     DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
@@ -162,16 +162,31 @@ struct Plan {
     std::vector<int> un_vert;     // ascending vertex ids
 };
 
-void build_plan(const int32_t* adj, int n_centres, int k, int V, int cluster_size, int n_threads, Plan& plan) {
-    // greedy region growing: a seed takes its nearest still-unassigned centres (adjacency rows are ordered
-    // by distance in the reference, the centre itself first)
+// Neighbourhood lists of one call: rectangular (n x k, the k-NN branch of get_adjacency_matrix,
+// searchlight.py:173) or ragged CSR (radius branch, searchlight.py:164-166).
+struct Rows {
+    const int32_t* data;
+    const int64_t* off;        // nullptr = rectangular
+    int k;                     // rectangular row length
+    const int32_t* anchors;    // optional: the vertex a centre sits on (used only to group centres spatially)
+    int n;
+    long row_off(int i) const { return off ? (long)off[i] : (long)i * k; }
+    const int32_t* row(int i) const { return data + row_off(i); }
+    int len(int i) const { return off ? (int)(off[i + 1] - off[i]) : k; }
+    int anchor(int i) const { return anchors ? anchors[i] : row(i)[0]; }
+    long total() const { return off ? (long)off[n] : (long)n * k; }
+};
+
+void build_plan(const Rows& rows, int V, int cluster_size, int n_threads, Plan& plan) {
+    // greedy region growing: a seed takes its nearest still-unassigned centres (k-NN adjacency rows are ordered
+    // by distance in the reference, the centre itself first; radius rows are in vertex order and scanned whole)
+    const int n_centres = rows.n;
     std::vector<int> centre_of(V, -1);
     for (int i = n_centres - 1; i >= 0; --i) {
-        const int v = adj[(long)i * k];
+        const int v = rows.anchor(i);
         if (v >= 0 && v < V) centre_of[v] = i;
     }
     std::vector<char> assigned(n_centres, 0);
-    const int reach = std::min(k, 3 * cluster_size);
     plan.cl_off.assign(1, 0);
     plan.members.clear();
     plan.members.reserve(n_centres);
@@ -180,7 +195,8 @@ void build_plan(const int32_t* adj, int n_centres, int k, int V, int cluster_siz
         assigned[s] = 1;
         plan.members.push_back(s);
         int count = 1;
-        const int32_t* row = adj + (long)s * k;
+        const int32_t* row = rows.row(s);
+        const int reach = rows.off ? rows.len(s) : std::min(rows.k, 3 * cluster_size);
         for (int j = 0; j < reach && count < cluster_size; ++j) {
             const int v = row[j];
             if (v < 0 || v >= V) continue;
@@ -205,7 +221,8 @@ void build_plan(const int32_t* adj, int n_centres, int k, int V, int cluster_siz
             if (c >= n_clusters) break;
             std::vector<int>& u = unions[c];
             for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) {
-                const int32_t* row = adj + (long)plan.members[m] * k;
+                const int32_t* row = rows.row(plan.members[m]);
+                const int k = rows.len(plan.members[m]);
                 for (int j = 0; j < k; ++j) {
                     const int v = row[j];
                     if (v < 0 || v >= V) continue;       // reported by the device-side check
@@ -255,11 +272,12 @@ int run_xty(mmd_handle* h) {
 }
 
 // One batch = clusters [c0, c1).  `slot0` = first output slot when yhat_only (diagnostic) is set.
-int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, double alpha, bool with_null) {
+int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1, int k_max, int kp, double alpha,
+              bool with_null) {
     const int n_cl = c1 - c0;
     const int t0 = plan.cl_off[c0], n_tasks = plan.cl_off[c1] - t0;
-    std::vector<int> task_row(n_tasks), task_un_n(n_tasks);
-    std::vector<long> task_un_off(n_tasks);
+    std::vector<int> task_k(n_tasks), task_un_n(n_tasks);
+    std::vector<long> task_row_off(n_tasks), task_un_off(n_tasks);
     std::vector<CentreTask> tasks(n_tasks);
     std::vector<GemmProblem> probs(n_cl);
     size_t pool_doubles = 0;
@@ -278,7 +296,8 @@ int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, do
         p.lower_only = 1;
         for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) {
             const int t = m - t0;
-            task_row[t] = plan.members[m];
+            task_row_off[t] = rows.row_off(plan.members[m]);
+            task_k[t] = rows.len(plan.members[m]);
             task_un_off[t] = plan.un_off[c];
             task_un_n[t] = u;
             CentreTask& ct = tasks[t];
@@ -287,6 +306,8 @@ int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, do
             ct.loc = h->loc.as<int>() + (long)t * kp;
             ct.nbr = h->nbr_sorted.as<int>() + (long)t * kp;
             ct.centre = plan.members[m];
+            ct.k = task_k[t];
+            ct.kp = round_up(task_k[t], NB);
         }
         pool_doubles += (size_t)u * ldu;
         max_u = std::max(max_u, u);
@@ -297,16 +318,17 @@ int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, do
         h->syrk_flops += 2.0 * tiles * 128.0 * 64.0 * h->ldt;
     }
     if (pool_doubles * sizeof(double) > h->gram_pool.bytes) return fail(h, "internal: gram pool too small");
-    if (to_device(h, h->task_row, task_row.data(), n_tasks)) return 1;
+    if (to_device(h, h->task_row, task_row_off.data(), n_tasks)) return 1;
+    if (to_device(h, h->task_k, task_k.data(), n_tasks)) return 1;
     if (to_device(h, h->task_union_off, task_un_off.data(), n_tasks)) return 1;
     if (to_device(h, h->task_union_n, task_un_n.data(), n_tasks)) return 1;
     if (to_device(h, h->tasks, tasks.data(), n_tasks)) return 1;
     if (to_device(h, h->probs, probs.data(), n_cl)) return 1;
 
     span_begin(h, ST_PREP);
-    CU(launch_prep_tasks(h->adj.as<int>(), k, kp, h->task_row.as<int>(), h->task_union_off.as<long>(),
-                         h->task_union_n.as<int>(), h->union_vertices.as<int>(), h->V, n_tasks,
-                         h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
+    CU(launch_prep_tasks(h->adj.as<int>(), h->task_row.as<long>(), h->task_k.as<int>(), k_max, kp,
+                         h->task_union_off.as<long>(), h->task_union_n.as<int>(), h->union_vertices.as<int>(), h->V,
+                         n_tasks, h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
     span_end(h);
 
     span_begin(h, ST_SYRK);
@@ -316,8 +338,7 @@ int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, do
     SolveParams sp{};
     sp.tasks = h->tasks.as<CentreTask>();
     sp.n_tasks = n_tasks;
-    sp.k = k;
-    sp.kp = kp;
+    sp.kp_max = kp;
     sp.alpha = alpha;
     sp.Xe = h->Xe.as<__half>();
     sp.work = h->work.as<double>();
@@ -329,8 +350,7 @@ int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, do
     PredictParams pp{};
     pp.tasks = sp.tasks;
     pp.n_tasks = n_tasks;
-    pp.k = k;
-    pp.kp = kp;
+    pp.kp_max = kp;
     pp.work = h->work.as<double>();
     pp.XtY = h->XtY.as<double>();
     pp.Dp = h->Dp;
@@ -373,20 +393,27 @@ int run_batch(mmd_handle* h, const Plan& plan, int c0, int c1, int k, int kp, do
     return 0;
 }
 
-int run_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha, bool with_null = false) {
+int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_null = false) {
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight");
-    if (k < 1 || k > h->V) return fail(h, "k=%d out of range (1..%d)", k, h->V);
-    if (k > h->n_train)
-        return fail(h, "k=%d exceeds n_train=%d: the primal normal equations are rank deficient only through "
-                       "alpha; the dual form is not implemented on this path", k, h->n_train);
-    if (k > 2000) return fail(h, "k=%d exceeds the supported maximum of 2000", k);
-    const int kp = round_up(k, NB);
+    const int n_centres = rows.n;
+    int k_max = 0;
+    for (int i = 0; i < n_centres; ++i) {
+        const int k = rows.len(i);
+        if (k < 1 || k > h->V) return fail(h, "k=%d out of range (1..%d) for centre %d", k, h->V, i);
+        if (k > h->n_train)
+            return fail(h, "k=%d exceeds n_train=%d: the primal normal equations are rank deficient only through "
+                           "alpha; the dual form is not implemented on this path", k, h->n_train);
+        if (k > 2000) return fail(h, "k=%d exceeds the supported maximum of 2000", k);
+        k_max = std::max(k_max, k);
+        if (!rows.off) break;              // rectangular: one length
+    }
+    const int kp = round_up(k_max, NB);
     int n_threads = h->host_threads > 0 ? h->host_threads : (int)std::thread::hardware_concurrency();
     n_threads = std::max(1, std::min(n_threads, 32));
 
-    if (to_device(h, h->adj, adjacency, (size_t)n_centres * k)) return 1;
+    if (to_device(h, h->adj, rows.data, (size_t)rows.total())) return 1;
     Plan plan;
-    build_plan(adjacency, n_centres, k, h->V, h->cluster_size, n_threads, plan);
+    build_plan(rows, h->V, h->cluster_size, n_threads, plan);
     const int n_clusters = (int)plan.cl_off.size() - 1;
     h->n_clusters += n_clusters;
     if (to_device(h, h->union_vertices, plan.un_vert.data(), plan.un_vert.size())) return 1;
@@ -427,7 +454,29 @@ int run_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int 
     }
 
     for (size_t b = 0; b + 1 < batch_start.size(); ++b)
-        if (run_batch(h, plan, batch_start[b], batch_start[b + 1], k, kp, alpha, with_null)) return 1;
+        if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, alpha, with_null)) return 1;
+    return 0;
+}
+
+int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double* scores_out, int32_t* flags_out,
+                          const char* who) {
+    const int n_centres = rows.n;
+    if (run_searchlight(h, rows, alpha)) {
+        cudaStreamSynchronize(h->stream);
+        h->spans.clear();
+        h->events_used = 0;
+        return 1;
+    }
+    int bad = 0;
+    CU(cudaMemcpyAsync(&bad, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(scores_out, h->scores.p, (size_t)n_centres * MMD_N_SCORES * sizeof(double), cudaMemcpyDefault,
+                       h->stream));
+    if (flags_out)
+        CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    resolve_spans(h);
+    if (bad == 2) return fail(h, "%s: adjacency holds a vertex index outside [0, %d)", who, h->V);
+    if (bad == 1) return fail(h, "internal: neighbour missing from its cluster union");
     return 0;
 }
 
@@ -463,7 +512,7 @@ void mmd_destroy(mmd_handle* h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
-                      &h->task_row, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
+                      &h->task_row, &h->task_k, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
                       &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count};
@@ -549,6 +598,53 @@ int mmd_knn(mmd_handle* h, const double* coords, int n_vertices, int k, int q_be
     dcoords.release();
     didx.release();
     ddist.release();
+    return rc;
+}
+
+int mmd_radius_neighbors(mmd_handle* h, const double* coords, int n_vertices, double radius, int q_begin, int q_end,
+                         const int64_t* offsets, int32_t* counts_out, int32_t* indices_out) {
+    if (!h) return 1;
+    if (!coords) return fail(h, "mmd_radius_neighbors: null pointer");
+    if (q_begin < 0 || q_end > n_vertices || q_begin > q_end) return fail(h, "mmd_radius_neighbors: bad query range");
+    if (!(radius >= 0.0)) return fail(h, "mmd_radius_neighbors: radius must be >= 0");
+    const bool fill = indices_out != nullptr;
+    if (fill ? !offsets : !counts_out) return fail(h, "mmd_radius_neighbors: the count pass needs counts_out, the fill pass offsets");
+    CU(cudaSetDevice(h->device));
+    const size_t nq = (size_t)(q_end - q_begin);
+    if (nq == 0) return 0;
+    DevBuf dcoords, dout, doff;
+    const double* c_dev = coords;
+    int rc = 0;
+    do {
+        if (!is_device_ptr(coords)) {
+            if ((rc = to_device(h, dcoords, coords, (size_t)n_vertices * 3))) break;
+            c_dev = dcoords.as<double>();
+        }
+        span_begin(h, ST_KNN);
+        cudaError_t e;
+        size_t n_out;
+        if (!fill) {
+            n_out = nq;
+            if (dout.ensure(nq * sizeof(int)) != cudaSuccess) { rc = fail(h, "mmd_radius_neighbors: out of memory"); break; }
+            e = launch_radius_count(c_dev, n_vertices, radius, q_begin, q_end, dout.as<int>(), h->stream);
+        } else {
+            if (offsets[0] != 0) { rc = fail(h, "mmd_radius_neighbors: offsets[0] must be 0"); break; }
+            n_out = (size_t)offsets[nq];
+            static_assert(sizeof(long) == sizeof(int64_t), "offsets are passed to the kernel as long");
+            if ((rc = to_device(h, doff, reinterpret_cast<const long*>(offsets), nq + 1))) break;
+            if (dout.ensure(std::max<size_t>(n_out, 1) * sizeof(int)) != cudaSuccess) { rc = fail(h, "mmd_radius_neighbors: out of memory"); break; }
+            e = launch_radius_fill(c_dev, n_vertices, radius, q_begin, q_end, doff.as<long>(), dout.as<int>(), h->stream);
+        }
+        span_end(h);
+        if (e != cudaSuccess) { rc = fail(h, "radius launch failed: %s", cudaGetErrorString(e)); break; }
+        cudaMemcpyAsync(fill ? indices_out : counts_out, dout.p, n_out * sizeof(int), cudaMemcpyDeviceToHost, h->stream);
+        e = cudaStreamSynchronize(h->stream);
+        resolve_spans(h);
+        if (e != cudaSuccess) { rc = fail(h, "mmd_radius_neighbors failed: %s", cudaGetErrorString(e)); break; }
+    } while (0);
+    dcoords.release();
+    dout.release();
+    doff.release();
     return rc;
 }
 
@@ -657,30 +753,36 @@ int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int 
     if (n_centres == 0) return 0;
     if (is_device_ptr(adjacency)) return fail(h, "mmd_searchlight: adjacency must be a host pointer");
     CU(cudaSetDevice(h->device));
-    if (run_searchlight(h, adjacency, n_centres, k, alpha)) {
-        cudaStreamSynchronize(h->stream);
-        h->spans.clear();
-        h->events_used = 0;
-        return 1;
+    const Rows rows{adjacency, nullptr, k, nullptr, n_centres};
+    return searchlight_and_fetch(h, rows, alpha, scores_out, flags_out, "mmd_searchlight");
+}
+
+int mmd_searchlight_ragged(mmd_handle* h, const int32_t* indices, const int64_t* offsets, const int32_t* anchors,
+                           int n_centres, double alpha, double* scores_out, int32_t* flags_out) {
+    if (!h) return 1;
+    if (!indices || !offsets || !scores_out) return fail(h, "mmd_searchlight_ragged: null pointer");
+    if (n_centres < 0) return fail(h, "mmd_searchlight_ragged: negative centre count");
+    if (n_centres == 0) return 0;
+    if (is_device_ptr(indices) || is_device_ptr(offsets))
+        return fail(h, "mmd_searchlight_ragged: indices and offsets must be host pointers");
+    if (offsets[0] != 0) return fail(h, "mmd_searchlight_ragged: offsets[0] must be 0");
+    for (int i = 0; i < n_centres; ++i) {
+        if (offsets[i + 1] < offsets[i]) return fail(h, "mmd_searchlight_ragged: offsets must be non-decreasing");
+        if (offsets[i + 1] == offsets[i])
+            return fail(h, "mmd_searchlight_ragged: centre %d has an empty neighbourhood (sklearn's Ridge.fit rejects "
+                           "an array with 0 features)", i);
     }
-    int bad = 0;
-    CU(cudaMemcpyAsync(&bad, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaMemcpyAsync(scores_out, h->scores.p, (size_t)n_centres * MMD_N_SCORES * sizeof(double), cudaMemcpyDefault,
-                       h->stream));
-    if (flags_out)
-        CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    resolve_spans(h);
-    if (bad == 2) return fail(h, "mmd_searchlight: adjacency holds a vertex index outside [0, %d)", h->V);
-    if (bad == 1) return fail(h, "internal: neighbour missing from its cluster union");
-    return 0;
+    CU(cudaSetDevice(h->device));
+    const Rows rows{indices, offsets, 0, anchors, n_centres};
+    return searchlight_and_fetch(h, rows, alpha, scores_out, flags_out, "mmd_searchlight_ragged");
 }
 
 int mmd_predict_centre(mmd_handle* h, const int32_t* neighbours, int k, double alpha, double* yhat_out) {
     if (!h) return 1;
     if (!neighbours || !yhat_out) return fail(h, "mmd_predict_centre: null pointer");
     CU(cudaSetDevice(h->device));
-    if (run_searchlight(h, neighbours, 1, k, alpha)) {
+    const Rows one{neighbours, nullptr, k, nullptr, 1};
+    if (run_searchlight(h, one, alpha)) {
         cudaStreamSynchronize(h->stream);
         h->spans.clear();
         h->events_used = 0;
@@ -719,7 +821,8 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
         CU(cudaStreamSynchronize(h->stream));          // `internal` is pageable and goes out of scope
     }
     if (to_device(h, h->perm_im, perm_imagery, (size_t)n_perm * h->n_im)) return 1;
-    if (run_searchlight(h, adjacency, n_centres, k, alpha, true)) {
+    const Rows rows{adjacency, nullptr, k, nullptr, n_centres};
+    if (run_searchlight(h, rows, alpha, true)) {
         cudaStreamSynchronize(h->stream);
         h->spans.clear();
         h->events_used = 0;

@@ -31,6 +31,10 @@ constexpr int THREADS = 128;
 constexpr int NWARPS = THREADS / 32;
 constexpr int KC = 8;                 // k-values per pipeline chunk (one 64-byte row segment)
 constexpr int STAGES = 4;
+#ifndef MMD_FS_PAIRED
+#define MMD_FS_PAIRED 0
+#endif
+constexpr bool PAIRED = MMD_FS_PAIRED != 0;   // two pipeline chunks per CTA barrier in strip_gemm (measured slower: 4.90 vs 4.53 s / 2 hemispheres)
 constexpr int A_ROWS = NWARPS * 16;   // strip rows staged per chunk (one 16-row strip per warp)
 constexpr int A_STAGE = A_ROWS * KC;  // [row][k], 64-byte rows: conflict-free 16-byte fragment loads
 constexpr int LDB_NN = 66;            // [k][n] chunk rows: 64 doubles + 2 pad
@@ -91,20 +95,8 @@ __device__ __forceinline__ void strip_gemm(Frag<NBW>& acc, RowPtr a_row, const d
         cp_async16(dst + b_off1, b_ptr1 + c * b_step);
     };
     __syncthreads();                                   // previous users of the pipeline buffers are done
-    for (int s = 0; s < STAGES - 1; ++s) {
-        if (s < nchunks) load(s, s);
-        cp_async_commit();
-    }
-    init();
     const int a_slot = NBW == 8 ? warp : 0, nb0 = NBW == 8 ? 0 : warp * NBW;
-    for (int c = 0; c < nchunks; ++c) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        {
-            const int n = c + STAGES - 1;
-            if (n < nchunks) load(n % STAGES, n);
-            cp_async_commit();
-        }
+    auto compute = [&](int c) {
         const double* st = pipe + (c % STAGES) * STAGE_DOUBLES;
         const double2 a0 = *reinterpret_cast<const double2*>(st + (a_slot * 16 + fr) * KC + 2 * fk);
         const double2 a1 = *reinterpret_cast<const double2*>(st + (a_slot * 16 + 8 + fr) * KC + 2 * fk);
@@ -135,6 +127,43 @@ __device__ __forceinline__ void strip_gemm(Frag<NBW>& acc, RowPtr a_row, const d
                 dmma884(acc.v[0][q + e][0], acc.v[0][q + e][1], a0.y, by[e]);
                 dmma884(acc.v[1][q + e][0], acc.v[1][q + e][1], a1.y, by[e]);
             }
+        }
+    };
+    if (PAIRED) {
+        // two chunks per barrier (nchunks is even: K is a multiple of 64): half the barriers and wait_groups of
+        // the one-chunk schedule; the next pair is in flight while the current one is consumed
+        if (nchunks > 0) {
+            load(0, 0);
+            load(1, 1);
+        }
+        cp_async_commit();
+        init();
+        for (int c = 0; c < nchunks; c += 2) {
+            cp_async_wait<0>();
+            __syncthreads();
+            if (c + 2 < nchunks) {
+                load((c + 2) % STAGES, c + 2);
+                load((c + 3) % STAGES, c + 3);
+            }
+            cp_async_commit();
+            compute(c);
+            compute(c + 1);
+        }
+    } else {
+        for (int s = 0; s < STAGES - 1; ++s) {
+            if (s < nchunks) load(s, s);
+            cp_async_commit();
+        }
+        init();
+        for (int c = 0; c < nchunks; ++c) {
+            cp_async_wait<STAGES - 2>();
+            __syncthreads();
+            {
+                const int n = c + STAGES - 1;
+                if (n < nchunks) load(n % STAGES, n);
+                cp_async_commit();
+            }
+            compute(c);
         }
     }
     cp_async_wait<0>();
@@ -216,7 +245,7 @@ template <int NBW>
 __device__ __forceinline__ void strip_init(Frag<NBW>& acc, const CentreTask& task, const SolveParams& prm, bool is_eval,
                                            int row0, int col0, int lane) {
     const int fr = lane >> 2, fk = lane & 3;
-    const int k = prm.k;
+    const int k = task.k;
     int lj[NBW][2];
 #pragma unroll
     for (int nb = 0; nb < NBW; ++nb)
@@ -417,9 +446,9 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
     const int task_id = blockIdx.x;
     if (task_id >= prm.n_tasks) return;
     const CentreTask task = prm.tasks[task_id];
-    const int kp = prm.kp, nblk = kp / NB;
+    const int kp = task.kp, nblk = kp / NB;
     const long ld = kp;
-    double* M = prm.work + (long)task_id * (kp + EVAL_PAD) * ld;   // rows 0..kp-1: L ; rows kp..: W then Zt
+    double* M = prm.work + (long)task_id * (prm.kp_max + EVAL_PAD) * prm.kp_max;   // rows 0..kp-1: L ; rows kp..: W then Zt
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double* stage = pipe + warp * 8 * LDD;
     double* Dsm = pipe;
@@ -520,7 +549,7 @@ cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s) {
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    if (p.kp % NB != 0) return cudaErrorInvalidValue;
+    if (p.kp_max % NB != 0) return cudaErrorInvalidValue;
     factor_solve_kernel<<<p.n_tasks, THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }

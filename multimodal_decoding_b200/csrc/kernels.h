@@ -38,15 +38,16 @@ struct CentreTask {
     const int* loc;       // k ascending positions of this centre's neighbours inside the union
     const int* nbr;       // k vertex ids in the same (ascending) order
     int centre;           // output slot (index into scores / flags)
+    int k;                // this centre's neighbour count (ragged radius-mode neighbourhoods: searchlight.py:164-171)
+    int kp;               // k rounded up to a multiple of 64: order of this centre's padded normal matrix
 };
 struct SolveParams {
     const CentreTask* tasks;
     int n_tasks;
-    int k;                // neighbours per centre
-    int kp;               // k rounded up to a multiple of 64
+    int kp_max;           // largest task.kp of the launch; the per-task stride of `work` is (kp_max + EVAL_PAD) * kp_max
     double alpha;
     const __half* Xe;     // (V x EVAL_PAD) evaluation trials per vertex
-    double* work;         // per task: (kp + EVAL_PAD) x kp doubles
+    double* work;         // per task: (task.kp + EVAL_PAD) x task.kp doubles at the start of its stride
     int* flags;           // per task slot: 1 if a non-positive pivot was met
 };
 size_t factor_solve_smem_bytes();
@@ -56,8 +57,8 @@ cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s);
 struct PredictParams {
     const CentreTask* tasks;
     int n_tasks;
-    int k, kp;
-    const double* work;   // as above; Zt = rows kp.. of each task's block
+    int kp_max;           // stride of `work` as in SolveParams
+    const double* work;   // as above; Zt = rows task.kp.. of each task's block
     const double* XtY;    // (V x Dp)
     int Dp;               // feature count rounded up to 64
     double* yhat;         // per task: EVAL_PAD x Dp
@@ -101,9 +102,11 @@ cudaError_t launch_cosine_dist(const double* P, int np, const double* C, int nc,
 cudaError_t launch_pairwise_count(const double* dist, int r, int c, unsigned long long* count, cudaStream_t s);
 
 // ---- prep.cu -----------------------------------------------------------------------------
-cudaError_t launch_prep_tasks(const int* adjacency, int k, int kp, const int* task_row, const long* task_union_off,
-                              const int* task_union_n, const int* union_vertices, int n_vertices, int n_tasks,
-                              int* nbr_sorted, int* loc, int* bad_index_flag, cudaStream_t s);
+// task t reads its neighbour list adjacency[task_row_off[t] .. + task_k[t]) and writes kp_max-strided rows
+cudaError_t launch_prep_tasks(const int* adjacency, const long* task_row_off, const int* task_k, int k_max, int kp_max,
+                              const long* task_union_off, const int* task_union_n, const int* union_vertices,
+                              int n_vertices, int n_tasks, int* nbr_sorted, int* loc, int* bad_index_flag,
+                              cudaStream_t s);
 __global__ void gather_rows_f16_kernel(const __half* Y, long ldy, const int* rows, int n_rows, int D, __half* out,
                                        int n_out, int ld_out);
 
@@ -111,5 +114,11 @@ __global__ void gather_rows_f16_kernel(const __half* Y, long ldy, const int* row
 // coords: (V x 3) float64 device; queries q_begin..q_end-1 are rows of coords; outputs are indexed from q_begin.
 cudaError_t launch_knn(const double* coords, int V, int k, int q_begin, int q_end, int64_t* idx_out,
                        double* dist_out, int* overflow_flag, cudaStream_t s);
+
+// ---- radius.cu ---------------------------------------------------------------------------
+cudaError_t launch_radius_count(const double* coords, int V, double radius, int q_begin, int q_end, int* counts,
+                                cudaStream_t s);
+cudaError_t launch_radius_fill(const double* coords, int V, double radius, int q_begin, int q_end, const long* offsets,
+                               int* indices, cudaStream_t s);
 
 }  // namespace mmd

@@ -28,9 +28,9 @@ __global__ void __launch_bounds__(THREADS, 2) predict_kernel(PredictParams prm) 
 
     const int task_id = blockIdx.y;
     const CentreTask task = prm.tasks[task_id];
-    const int k = prm.k, kp = prm.kp, Dp = prm.Dp;
+    const int k = task.k, kp = task.kp, Dp = prm.Dp;
     const int d0 = blockIdx.x * BN;
-    const double* Zt = prm.work + (long)task_id * (kp + EVAL_PAD) * kp + (long)kp * kp;   // 144 x kp
+    const double* Zt = prm.work + (long)task_id * (prm.kp_max + EVAL_PAD) * prm.kp_max + (long)kp * kp;   // 144 x kp
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp & 1, wn = warp >> 1;           // 2 x 4 warps: 72 rows x 16 columns each
 
@@ -108,7 +108,7 @@ cudaError_t launch_predict(const PredictParams& p, cudaStream_t s) {
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    if (p.kp > 2048) return cudaErrorInvalidValue;
+    if (p.kp_max > 2048) return cudaErrorInvalidValue;
     dim3 grid(p.Dp / BN, p.n_tasks);
     predict_kernel<<<grid, THREADS, predict_smem_bytes(), s>>>(p);
     return cudaGetLastError();

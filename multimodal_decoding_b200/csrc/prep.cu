@@ -8,18 +8,20 @@
 
 namespace mmd {
 
-__global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__ adjacency, int k, int kp,
-                                                         const int* __restrict__ task_row,
+__global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__ adjacency,
+                                                         const long* __restrict__ task_row_off,
+                                                         const int* __restrict__ task_k, int kp,
                                                          const long* __restrict__ task_union_off,
                                                          const int* __restrict__ task_union_n,
                                                          const int* __restrict__ union_vertices, int n_vertices,
                                                          int* __restrict__ nbr_sorted, int* __restrict__ loc,
                                                          int* __restrict__ bad_index_flag) {
-    extern __shared__ int sm[];                 // next power of two >= k
+    extern __shared__ int sm[];                 // next power of two >= the largest k of the launch
     const int t = blockIdx.x, tid = threadIdx.x;
+    const int k = task_k[t];
     int np2 = 1;
     while (np2 < k) np2 <<= 1;
-    const int* row = adjacency + (long)task_row[t] * k;
+    const int* row = adjacency + task_row_off[t];
     for (int i = tid; i < np2; i += blockDim.x) {
         int v = i < k ? row[i] : 0x7fffffff;
         if (i < k && (v < 0 || v >= n_vertices)) {
@@ -62,12 +64,13 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
     }
 }
 
-cudaError_t launch_prep_tasks(const int* adjacency, int k, int kp, const int* task_row, const long* task_union_off,
-                              const int* task_union_n, const int* union_vertices, int n_vertices, int n_tasks,
-                              int* nbr_sorted, int* loc, int* bad_index_flag, cudaStream_t s) {
+cudaError_t launch_prep_tasks(const int* adjacency, const long* task_row_off, const int* task_k, int k_max, int kp_max,
+                              const long* task_union_off, const int* task_union_n, const int* union_vertices,
+                              int n_vertices, int n_tasks, int* nbr_sorted, int* loc, int* bad_index_flag,
+                              cudaStream_t s) {
     int np2 = 1;
-    while (np2 < k) np2 <<= 1;
-    prep_tasks_kernel<<<n_tasks, 256, np2 * sizeof(int), s>>>(adjacency, k, kp, task_row, task_union_off,
+    while (np2 < k_max) np2 <<= 1;
+    prep_tasks_kernel<<<n_tasks, 256, np2 * sizeof(int), s>>>(adjacency, task_row_off, task_k, kp_max, task_union_off,
                                                              task_union_n, union_vertices, n_vertices, nbr_sorted,
                                                              loc, bad_index_flag);
     return cudaGetLastError();

@@ -81,6 +81,24 @@ class Engine:
                                       idx.ctypes.data, dist.ctypes.data))
         return dist, idx
 
+    def radius_neighbors(self, coords, radius: float):
+        """The radius branch of get_adjacency_matrix (searchlight.py:164-166): a list with one int64 index array per
+        vertex (ascending vertex id, the vertex itself included)."""
+        coords = np.ascontiguousarray(np.asarray(coords, dtype=np.float64))
+        if coords.ndim != 2 or coords.shape[1] != 3:
+            raise ValueError("coords must be (n_vertices, 3)")
+        v = len(coords)
+        counts = np.zeros(v, dtype=np.int32)
+        self._check(self._lib.mmd_radius_neighbors(self._h, coords.ctypes.data, v, float(radius), 0, v, None,
+                                                   counts.ctypes.data, None))
+        offsets = np.zeros(v + 1, dtype=np.int64)
+        np.cumsum(counts, out=offsets[1:])
+        indices = np.empty(max(int(offsets[-1]), 1), dtype=np.int32)
+        self._check(self._lib.mmd_radius_neighbors(self._h, coords.ctypes.data, v, float(radius), 0, v,
+                                                   offsets.ctypes.data, None, indices.ctypes.data))
+        idx64 = indices[:offsets[-1]].astype(np.int64)
+        return [idx64[offsets[i]:offsets[i + 1]] for i in range(v)]
+
     # -- trials ------------------------------------------------------------------------------
     def upload(self, X, Y, train_ids, test_ids, imagery_ids, test_is_caption):
         n_total, n_vertices = X.shape
@@ -106,10 +124,38 @@ class Engine:
         del xk, yk
 
     # -- the hot path ------------------------------------------------------------------------
+    @staticmethod
+    def _is_ragged(adjacency):
+        if isinstance(adjacency, np.ndarray) and adjacency.dtype != object:
+            return adjacency.ndim != 2
+        lens = {len(r) for r in adjacency}
+        return len(lens) > 1
+
+    def searchlight_ragged(self, adjacency, alpha: float = 1.0, anchors=None):
+        """Radius-mode neighbourhoods (searchlight.py:164-171): `adjacency` is a sequence of index arrays of
+        different lengths.  `anchors[i]` = the vertex centre i sits on (default: i when there is one centre per
+        vertex, else the first entry of each list); it only steers the grouping of centres, never the result."""
+        rows = [np.asarray(r, dtype=np.int32).ravel() for r in adjacency]
+        n = len(rows)
+        offsets = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum([len(r) for r in rows], out=offsets[1:])
+        indices = np.ascontiguousarray(np.concatenate(rows)) if n else np.zeros(0, dtype=np.int32)
+        anc = None if anchors is None else np.ascontiguousarray(np.asarray(anchors, dtype=np.int32))
+        if anc is not None and len(anc) != n:
+            raise ValueError("anchors must have one entry per centre")
+        scores = np.empty((n, _lib.N_SCORES), dtype=np.float64)
+        flags = np.zeros(n, dtype=np.int32)
+        self._check(self._lib.mmd_searchlight_ragged(self._h, indices.ctypes.data, offsets.ctypes.data,
+                                                     None if anc is None else anc.ctypes.data, n, float(alpha),
+                                                     scores.ctypes.data, flags.ctypes.data))
+        return scores, flags
+
     def searchlight(self, adjacency, alpha: float = 1.0):
+        if self._is_ragged(adjacency):
+            return self.searchlight_ragged(adjacency, alpha)
         adj = np.ascontiguousarray(np.asarray(adjacency, dtype=np.int32))
         if adj.ndim != 2:
-            raise ValueError("adjacency must be rectangular (n_centres, k); ragged radius mode is not supported")
+            raise ValueError("adjacency must be a sequence of index arrays")
         n, k = adj.shape
         scores = np.empty((n, _lib.N_SCORES), dtype=np.float64)
         flags = np.zeros(n, dtype=np.int32)

@@ -22,6 +22,8 @@ their documented algorithms (reference pins: scikit-learn 1.0.2, scipy 1.11.4, n
 * `scipy.spatial.distance.cdist(a, b, "cosine")`: 1 - a.b / (|a| |b|) (call site `eval.py:104`).
 * `sklearn.neighbors.NearestNeighbors().kneighbors`: exact Euclidean k-NN, ascending distance,
   the query point itself first (call site `searchlight.py:173`).
+* `NearestNeighbors(radius=r).radius_neighbors_graph(coords)`: every point within Euclidean distance r,
+  tested on the squared distance (call site `searchlight.py:164-165`).
 * `sklearn.model_selection.KFold(5)` folds and GridSearchCV's first-best selection
   (call site `ridge_regression_decoding.py:111-117`).
 """
@@ -196,6 +198,23 @@ def knn_adjacency(coords, k: int, block: int = 2048):
 # ------------------------------------------------------------------------------------------
 # null distribution (searchlight.py:61-79, data.py:540-561)
 # ------------------------------------------------------------------------------------------
+def radius_adjacency(coords, radius: float, block: int = 2048):
+    """Radius branch of get_adjacency_matrix (searchlight.py:160-166): for every point the ascending indices of all
+    points (itself included) with squared distance ((dx*dx + dy*dy) + dz*dz) <= radius*radius -- the kd-tree's
+    reduced-distance test of sklearn's `radius_neighbors_graph`.  Returns a list of int64 arrays."""
+    c = np.asarray(coords, dtype=np.float64)
+    r2 = float(radius) * float(radius)
+    out = []
+    for s in range(0, len(c), block):
+        q = c[s:s + block]
+        dx = q[:, None, 0] - c[None, :, 0]
+        dy = q[:, None, 1] - c[None, :, 1]
+        dz = q[:, None, 2] - c[None, :, 2]
+        inside = ((dx * dx + dy * dy) + dz * dz) <= r2
+        out.extend(np.flatnonzero(row).astype(np.int64) for row in inside)
+    return out
+
+
 def shuffled_test_indices(n_permutations: int, n_test: int = 140):
     """create_null_distr_shuffled_indices (data.py:540-561): legacy numpy RandomState seeds
     0,1,2,...; each half permuted on its own; draws with any fixed point are skipped."""

@@ -4,7 +4,7 @@ Run from the repo root inside the build container (needs /root/reference):
 
     python tests/golden/make_golden.py
 
-Outputs (committed):  searchlight_small.npz, searchlight_smooth.npz, knn_small.npz,
+Outputs (committed):  searchlight_small.npz, searchlight_smooth.npz, searchlight_radius.npz, knn_small.npz,
 eval_cases.npz, null_distr_small.npz, gridsearch_small.npz.
 Each file stores the exact inputs next to the reference outputs so the tests never depend on
 random-stream stability.
@@ -64,6 +64,30 @@ def knn_case():
     np.savez_compressed(os.path.join(HERE, "knn_small.npz"), coords=mesh.coords, adjacency=adj.astype(np.int32),
                         distances=dist, coords2=mesh2.coords, adjacency2=adj2.astype(np.int32), distances2=dist2)
     print("knn", adj.shape, adj2.shape)
+
+
+def radius_case():
+    """Radius-mode neighbourhoods exactly as searchlight.py:160-166 builds them, then the unmodified loop on the
+    ragged adjacency."""
+    mesh = syn.make_mesh(level=3, seed=13)
+    trials = syn.make_trials(mesh, n_train=200, n_dims=48, n_factors=8, iid=False, seed=5, signal=0.6)
+    inp = syn.make_searchlight_inputs(mesh, trials)
+    radius = 63.0
+    nn = NearestNeighbors(radius=radius)
+    adjacency = [np.argwhere(arr == 1)[:, 0] for arr in
+                 nn.fit(inp.coords).radius_neighbors_graph(inp.coords).toarray()]      # searchlight.py:164-165
+    lens = np.array([len(a) for a in adjacency])
+    scores = ref_sl.custom_search_light(
+        inp.X, inp.latents, estimator=Ridge(alpha=1.0, fit_intercept=False), A=adjacency,
+        train_ids=inp.train_ids, test_ids=inp.test_ids, imagery_ids=inp.imagery_ids, n_jobs=1)
+    out = scores_to_array(scores)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    np.savez_compressed(os.path.join(HERE, "searchlight_radius.npz"), X=inp.X, latents=inp.latents,
+                        indices=np.concatenate(adjacency).astype(np.int32), offsets=offsets, coords=inp.coords,
+                        radius=radius, n_train=len(inp.train_ids), n_test=len(inp.test_ids),
+                        n_imagery=len(inp.imagery_ids), alpha=1.0, scores=out, keys=np.array(KEYS))
+    print("radius", out.shape, "neighbours min/mean/max", lens.min(), lens.mean().round(1), lens.max(),
+          "mean", out.mean(0).round(3))
 
 
 def eval_cases():
@@ -161,6 +185,7 @@ if __name__ == "__main__":
     searchlight_case("searchlight_captions.npz", level=3, k=33, n_train=400, n_dims=32, alpha=10.0, iid=False,
                      seed=2, training_mode="captions")
     knn_case()
+    radius_case()
     eval_cases()
     null_distr_case()
     gridsearch_case()

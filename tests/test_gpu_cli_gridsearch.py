@@ -72,3 +72,40 @@ def test_searchlight_cli_run(tmp_path, monkeypatch):
         assert np.array_equal(res["adjacency"], a_ref)
     finally:
         d.set_data_provider(d.SyntheticProvider())
+
+
+def test_searchlight_cli_run_radius(tmp_path, monkeypatch):
+    """`--radius` (searchlight.py:164-171): ragged adjacency in the pickle, per-vertex neighbour counts, scores
+    against the oracle."""
+    from multimodal_decoding_b200 import data as d
+    import multimodal_decoding_b200.analyses.decoding.searchlight.searchlight as sl
+    monkeypatch.setattr(sl, "SEARCHLIGHT_OUT_DIR", str(tmp_path))
+    d.set_data_provider(d.SyntheticProvider(n_train=300, nan_fraction=0.08, seed=5))
+    try:
+        args = sl.get_args(["--model", "clip", "--radius", "50", "--training-mode", "agnostic", "--subjects", "sub-01",
+                            "--hemis", "left", "--resolution", "fsaverage3"])
+        sl.run(args)
+        cfg = d.LatentFeatsConfig("clip", logging=False)
+        path = sl.get_results_file_path(cfg, "left", "sub-01", "agnostic", "fsaverage3", "radius_50.0", 1)
+        res = pickle.load(open(path, "rb"))
+        V = int((~res["nan_locations"]).sum())
+        coords = d.get_data_provider().mesh("left", "fsaverage3").coords[~res["nan_locations"]]
+        want_A = orc.radius_adjacency(coords, 50.0)
+        assert len(res["adjacency"]) == V and res["distances"] is None
+        assert all(np.array_equal(a, b) for a, b in zip(res["adjacency"], want_A))
+        assert res["n_neighbors"] == [len(a) for a in want_A] and len(set(res["n_neighbors"])) > 1
+        tr_f, _, _ = d.get_fmri_surface_data("", "sub-01", d.SPLIT_TRAIN, "agnostic", "left", "fsaverage3")
+        te_f, _, _ = d.get_fmri_surface_data("", "sub-01", d.SPLIT_TEST, hemi="left", resolution="fsaverage3")
+        im_f, _, _ = d.get_fmri_surface_data("", "sub-01", d.SPLIT_IMAGERY, hemi="left", resolution="fsaverage3")
+        tr_f, te_f, im_f = d.standardize_fmri_betas(tr_f, te_f, im_f)
+        lat = [d.get_latent_features(cfg, "sub-01", s) for s in (d.SPLIT_TRAIN, d.SPLIT_TEST, d.SPLIT_IMAGERY)]
+        lat = np.concatenate(d.standardize_latents(*lat)).astype(np.float16)
+        X = np.concatenate((tr_f, te_f, im_f)).astype(np.float16)
+        ntr, nte = len(tr_f), len(te_f)
+        ids = (np.arange(ntr), np.arange(ntr, ntr + nte), np.arange(ntr + nte, ntr + nte + len(im_f)))
+        centres = list(range(0, V, 29))
+        want = orc.search_light(X, lat, want_A, *ids, 1.0, orc.default_is_caption(nte), centres)
+        got = np.array([[res["scores"][c][k] for k in orc.SCORE_KEYS] for c in centres])
+        assert np.array_equal(got, want)
+    finally:
+        d.set_data_provider(d.SyntheticProvider())

@@ -158,3 +158,60 @@ def test_errors(engine, golden_dir):
         engine.upload(g["X"].astype(np.float32), g["latents"], tr, te, im, orc.default_is_caption(len(te)))
     scores, _ = engine.searchlight(g["adjacency"][:0], 1.0)
     assert scores.shape == (0, 8)
+
+
+# ---- radius mode: ragged neighbourhoods (searchlight.py:164-171) ---------------------------------------------
+def _ragged(g):
+    off = g["offsets"]
+    return [g["indices"][off[i]:off[i + 1]].astype(np.int64) for i in range(len(off) - 1)]
+
+
+def test_radius_neighbours_bit_exact(engine, golden_dir):
+    g = np.load(os.path.join(golden_dir, "searchlight_radius.npz"))
+    want = _ragged(g)
+    got = engine.radius_neighbors(g["coords"], float(g["radius"]))
+    assert len(got) == len(want)
+    assert all(a.dtype == np.int64 and np.array_equal(a, b) for a, b in zip(got, want))
+    # radius 0: every vertex is its own only neighbour
+    assert all(np.array_equal(a, [i]) for i, a in enumerate(engine.radius_neighbors(g["coords"][:50], 0.0)))
+
+
+def test_ragged_searchlight_matches_reference_fixture(engine, golden_dir):
+    g = np.load(os.path.join(golden_dir, "searchlight_radius.npz"))
+    tr, te, im = _ids(g)
+    A = _ragged(g)
+    engine.upload(g["X"], g["latents"], tr, te, im, orc.default_is_caption(len(te)))
+    for anchors in (np.arange(len(A)), None):          # grouping hint must not change the result
+        scores, flags = engine.searchlight_ragged(A, float(g["alpha"]), anchors)
+        assert flags.sum() == 0
+        assert np.abs(scores - g["scores"]).max() <= TOL
+        assert np.array_equal(scores, g["scores"])
+    # a subset of centres in arbitrary order, dispatched from searchlight() on a list input
+    pick = [5, 300, 17, 641, 2]
+    scores, _ = engine.searchlight([A[i] for i in pick], float(g["alpha"]))
+    assert np.array_equal(scores, g["scores"][pick])
+
+
+def test_ragged_errors(engine, golden_dir):
+    g = np.load(os.path.join(golden_dir, "searchlight_radius.npz"))
+    tr, te, im = _ids(g)
+    engine.upload(g["X"], g["latents"], tr, te, im, orc.default_is_caption(len(te)))
+    with pytest.raises(RuntimeError, match="empty neighbourhood"):
+        engine.searchlight_ragged([np.array([1, 2, 3]), np.array([], dtype=np.int64)], 1.0)
+    with pytest.raises(RuntimeError, match="outside"):
+        engine.searchlight_ragged([np.array([1, 2, 3]), np.array([0, 10 ** 6])], 1.0)
+    with pytest.raises(RuntimeError, match="exceeds n_train"):
+        engine.searchlight_ragged([np.arange(len(tr) + 1), np.array([0, 1])], 1.0)
+
+
+def test_dropin_custom_search_light_ragged(golden_dir):
+    """The reference-facing call with the radius-mode adjacency list (searchlight.py:117-149)."""
+    from sklearn.linear_model import Ridge
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+    g = np.load(os.path.join(golden_dir, "searchlight_radius.npz"))
+    tr, te, im = _ids(g)
+    out = sl.custom_search_light(g["X"], g["latents"], Ridge(alpha=float(g["alpha"]), fit_intercept=False), _ragged(g),
+                                 list(tr), list(te), list(im), n_jobs=1)
+    assert out.shape == (len(g["scores"]),) and out.dtype == object
+    got = np.array([[d[k] for k in g["keys"]] for d in out])
+    assert np.array_equal(got, g["scores"])

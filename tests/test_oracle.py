@@ -34,6 +34,25 @@ def test_knn_matches_sklearn_kdtree(golden_dir):
         assert np.array_equal(idx[:, 0], np.arange(len(idx)))
 
 
+def _ragged(g):
+    off = g["offsets"]
+    return [g["indices"][off[i]:off[i + 1]].astype(np.int64) for i in range(len(off) - 1)]
+
+
+def test_radius_mode_matches_reference(golden_dir):
+    """searchlight.py:164-166 neighbourhoods and the loop on the ragged adjacency."""
+    g = _load(golden_dir, "searchlight_radius.npz")
+    A = _ragged(g)
+    got_A = orc.radius_adjacency(g["coords"], float(g["radius"]))
+    assert len(got_A) == len(A) and all(np.array_equal(a, b) for a, b in zip(got_A, A))
+    assert len({len(a) for a in A}) > 1 and min(map(len, A)) < 64 < max(map(len, A))   # two padded sizes
+    ntr, nte, nim = int(g["n_train"]), int(g["n_test"]), int(g["n_imagery"])
+    tr, te, im = np.arange(ntr), np.arange(ntr, ntr + nte), np.arange(ntr + nte, ntr + nte + nim)
+    centres = list(range(0, len(A), 4))
+    got = orc.search_light(g["X"], g["latents"], A, tr, te, im, alpha=float(g["alpha"]), centres=centres)
+    assert np.array_equal(got, g["scores"][centres]), np.abs(got - g["scores"][centres]).max()
+
+
 def test_eval_known_answers(golden_dir):
     g = _load(golden_dir, "eval_cases.npz")
     lat, pred, im_lat, im_pred = g["lat"], g["pred"], g["im_lat"], g["im_pred"]
