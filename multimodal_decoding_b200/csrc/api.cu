@@ -70,7 +70,7 @@ struct mmd_handle {
     // uploaded problem
     int V = 0, n_train = 0, ldt = 0, n_test = 0, n_cap = 0, n_img = 0, n_im = 0, D = 0, Dp = 0;
     bool uploaded = false;
-    DevBuf Xt, Xe, Yt, cand, cand_sq, XtY;
+    DevBuf Xt, Xe, Yt, cand, cand64, cand_sq, XtY;
     // per-call / per-batch workspaces
     DevBuf adj, union_vertices, task_row, task_k, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
@@ -79,7 +79,7 @@ struct mmd_handle {
     int n_perm = 0;
     std::vector<int> int_of_test;   // position in test_ids order -> internal evaluation row (captions first)
     // knobs
-    int cluster_size = 128, batch_centres = 2048, host_threads = 0;
+    int cluster_size = 256, batch_centres = 2048, host_threads = 0;
     // stats
     float stage_ms[MMD_N_STAGES] = {0};
     int64_t launches = 0, n_clusters = 0;
@@ -273,7 +273,7 @@ int run_xty(mmd_handle* h) {
 
 // One batch = clusters [c0, c1).  `slot0` = first output slot when yhat_only (diagnostic) is set.
 int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1, int k_max, int kp, double alpha,
-              bool with_null) {
+              bool with_null, bool raw_yhat) {
     const int n_cl = c1 - c0;
     const int t0 = plan.cl_off[c0], n_tasks = plan.cl_off[c1] - t0;
     std::vector<int> task_k(n_tasks), task_un_n(n_tasks);
@@ -355,6 +355,10 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     pp.XtY = h->XtY.as<double>();
     pp.Dp = h->Dp;
     pp.yhat = h->yhat.as<double>();
+    pp.n_cap = h->n_cap;
+    pp.n_img = h->n_img;
+    pp.n_im = h->n_im;
+    pp.standardize = raw_yhat ? 0 : 1;
     span_begin(h, ST_PREDICT);
     CU(launch_predict(pp, h->stream));
     span_end(h);
@@ -364,7 +368,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     sc.n_tasks = n_tasks;
     sc.yhat = h->yhat.as<double>();
     sc.Dp = h->Dp;
-    sc.cand = h->cand.as<__half>();
+    sc.cand = h->cand64.as<double>();
     sc.cand_sq = h->cand_sq.as<double>();
     sc.n_cap = h->n_cap;
     sc.n_img = h->n_img;
@@ -393,7 +397,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     return 0;
 }
 
-int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_null = false) {
+int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_null = false, bool raw_yhat = false) {
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight");
     const int n_centres = rows.n;
     int k_max = 0;
@@ -440,7 +444,7 @@ int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_nul
 
     CU(h->gram_pool.ensure(max_pool * sizeof(double)));
     CU(h->work.ensure((size_t)max_tasks * (kp + EVAL_PAD) * kp * sizeof(double)));
-    CU(h->yhat.ensure((size_t)max_tasks * EVAL_PAD * h->Dp * sizeof(double)));
+    CU(h->yhat.ensure((size_t)max_tasks * YHAT_ROWS * h->Dp * sizeof(double)));
     CU(h->nbr_sorted.ensure((size_t)max_tasks * kp * sizeof(int)));
     CU(h->loc.ensure((size_t)max_tasks * kp * sizeof(int)));
     CU(h->scores.ensure((size_t)n_centres * MMD_N_SCORES * sizeof(double)));
@@ -454,7 +458,7 @@ int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_nul
     }
 
     for (size_t b = 0; b + 1 < batch_start.size(); ++b)
-        if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, alpha, with_null)) return 1;
+        if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, alpha, with_null, raw_yhat)) return 1;
     return 0;
 }
 
@@ -511,7 +515,7 @@ void mmd_destroy(mmd_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
+    DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
                       &h->task_row, &h->task_k, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
                       &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
@@ -714,6 +718,7 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
         CUB(h->Xe.ensure((size_t)n_vertices * EVAL_PAD * sizeof(__half)));
         CUB(h->Yt.ensure((size_t)h->Dp * h->ldt * sizeof(__half)));
         CUB(h->cand.ensure((size_t)EVAL_PAD * h->Dp * sizeof(__half)));
+        CUB(h->cand64.ensure((size_t)EVAL_PAD * h->Dp * sizeof(double)));
         CUB(h->cand_sq.ensure((size_t)EVAL_PAD * sizeof(double)));
         CUB(h->XtY.ensure((size_t)n_vertices * h->Dp * sizeof(double)));
         CUB(cudaMemsetAsync(h->Yt.p, 0, (size_t)h->Dp * h->ldt * sizeof(__half), h->stream));
@@ -731,7 +736,8 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
             row_sqnorm_kernel<<<EVAL_PAD, 128, 0, h->stream>>>(h->cand.as<__half>(), h->Dp, h->tmp.as<int>(), EVAL_PAD,
                                                               h->Dp, h->cand_sq.as<double>());
         }
-        span_end(h, 5);
+        half_to_double_kernel<<<148, 256, 0, h->stream>>>(h->cand.as<__half>(), h->cand64.as<double>(), (long)EVAL_PAD * h->Dp);
+        span_end(h, 6);
         CUB(cudaGetLastError());
         if ((rc = run_xty(h))) break;
         CUB(cudaStreamSynchronize(h->stream));
@@ -782,7 +788,7 @@ int mmd_predict_centre(mmd_handle* h, const int32_t* neighbours, int k, double a
     if (!neighbours || !yhat_out) return fail(h, "mmd_predict_centre: null pointer");
     CU(cudaSetDevice(h->device));
     const Rows one{neighbours, nullptr, k, nullptr, 1};
-    if (run_searchlight(h, one, alpha)) {
+    if (run_searchlight(h, one, alpha, false, true)) {
         cudaStreamSynchronize(h->stream);
         h->spans.clear();
         h->events_used = 0;

@@ -11,6 +11,7 @@ namespace mmd {
 void launch_pack_transpose(const __half* X, long ldx, const int* ids_dev, int n_ids, int V, __half* out,
                            int ld_out, cudaStream_t s);
 __global__ void row_sqnorm_kernel(const __half* Y, long ldy, const int* rows, int n_rows, int D, double* sq);
+__global__ void half_to_double_kernel(const __half* in, double* out, long n);
 
 // ---- gemm_gather.cu ----------------------------------------------------------------------
 struct GemmProblem {
@@ -61,8 +62,18 @@ struct PredictParams {
     const double* work;   // as above; Zt = rows task.kp.. of each task's block
     const double* XtY;    // (V x Dp)
     int Dp;               // feature count rounded up to 64
-    double* yhat;         // per task: EVAL_PAD x Dp
+    double* yhat;         // per task: YHAT_ROWS x Dp (layout below)
+    int n_cap, n_img, n_im;
+    int standardize;      // 1: rows are z-scored per prediction group (the scoring input); 0: raw predictions
 };
+// Rows of a task's yhat block, written by predict and read by score:
+//   0 .. n_eval-1            predictions of [caption test | image test | imagery] trials; with `standardize` each
+//                            group is z-scored per feature (StandardScaler semantics: ddof 0, scale 1 if the
+//                            variance is 0; eval.py:118 through calc_all_pairwise_accuracy_scores)
+//   n_eval .. EVAL_PAD-1     zero
+//   EVAL_PAD .. +n_im-1      the un-standardised imagery predictions (the *_no_std scores, searchlight.py:84-87)
+//   .. YHAT_ROWS-1           zero
+constexpr int YHAT_ROWS = 152;
 size_t predict_smem_bytes();
 cudaError_t launch_predict(const PredictParams& p, cudaStream_t s);
 
@@ -70,9 +81,9 @@ cudaError_t launch_predict(const PredictParams& p, cudaStream_t s);
 struct ScoreParams {
     const CentreTask* tasks;
     int n_tasks;
-    const double* yhat;        // per task EVAL_PAD x Dp; rows: captions, images, imagery, zero pad
+    const double* yhat;        // per task YHAT_ROWS x Dp, standardised by predict (layout at PredictParams)
     int Dp;
-    const __half* cand;        // (EVAL_PAD x Dp) candidate latents, rows ordered like yhat rows
+    const double* cand;        // (EVAL_PAD x Dp) candidate latents as float64, rows ordered like yhat rows
     const double* cand_sq;     // squared norms of the candidate rows
     int n_cap, n_img, n_im;
     double* scores;            // (n_centres x 8), written at row task.centre

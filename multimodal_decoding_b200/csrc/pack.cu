@@ -57,4 +57,9 @@ __global__ void row_sqnorm_kernel(const __half* __restrict__ Y, long ldy, const 
     }
 }
 
+// out[i] = (double)in[i]: the candidate latents as float64 operands of the scoring GEMM (exact widening)
+__global__ void half_to_double_kernel(const __half* __restrict__ in, double* __restrict__ out, long n) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) out[i] = h2d(in[i]);
+}
+
 }  // namespace mmd

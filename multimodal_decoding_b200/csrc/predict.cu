@@ -16,6 +16,9 @@ constexpr int LDA = KC + 4;          // 20 doubles: conflict-free A fragments
 constexpr int LDB = BN + 4;          // 68 doubles: conflict-free B fragments
 constexpr int STAGES = 3;
 constexpr int A_STAGE = EVAL_PAD * LDA, B_STAGE = KC * LDB;   // doubles
+constexpr int LDT = BN + 2;          // epilogue tile stride (even: rows stay 16-byte aligned for the double2 stores)
+static_assert(STAGES * (A_STAGE + B_STAGE) >= EVAL_PAD * LDT + 4 * BN, "the epilogue tile aliases the pipeline buffers");
+static_assert(THREADS == 4 * BN, "epilogue thread map: 4 row quarters x 64 columns");
 }  // namespace
 
 size_t predict_smem_bytes() { return (size_t)STAGES * (A_STAGE + B_STAGE) * sizeof(double) + 2048 * sizeof(int); }
@@ -88,7 +91,54 @@ __global__ void __launch_bounds__(THREADS, 2) predict_kernel(PredictParams prm) 
     }
     cp_async_wait<0>();
 
-    double* out = prm.yhat + (long)task_id * EVAL_PAD * Dp;
+    double* out = prm.yhat + (long)task_id * YHAT_ROWS * Dp;
+    const int n_cap = prm.n_cap, n_test = prm.n_cap + prm.n_img, n_eval = n_test + prm.n_im;
+    if (prm.standardize) {
+        // Per-feature z-scoring of the three prediction groups before the tile leaves the SM: the CTA holds all 144
+        // rows of its 64 columns.  The tile is parked in the (now idle) pipeline buffers so the accumulator registers
+        // die here; then two exact passes per group (mean, centred sum of squares) like StandardScaler.
+        __syncthreads();
+        double* T = As;                                    // [EVAL_PAD][LDT]
+        double* red = T + EVAL_PAD * LDT;                  // [4][BN]
+#pragma unroll
+        for (int i = 0; i < 9; ++i)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                *reinterpret_cast<double2*>(T + (wm * 72 + i * 8 + fr) * LDT + wn * 16 + j * 8 + 2 * fk) =
+                    make_double2(acc[i][j][0], acc[i][j][1]);
+        __syncthreads();
+        const int c = tid & (BN - 1), q = tid >> 6;        // column of the tile, quarter of the rows
+        const int lo[3] = {0, n_cap, n_test}, hi[3] = {n_cap, n_test, n_eval};
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+            const int n_g = hi[g] - lo[g];
+            double s = 0.0;
+            for (int r = lo[g] + q; r < hi[g]; r += 4) s += T[r * LDT + c];
+            red[q * BN + c] = s;
+            __syncthreads();
+            const double mu = n_g > 0 ? (((red[c] + red[BN + c]) + red[2 * BN + c]) + red[3 * BN + c]) / n_g : 0.0;
+            __syncthreads();
+            double v = 0.0;
+            for (int r = lo[g] + q; r < hi[g]; r += 4) {
+                const double t = T[r * LDT + c] - mu;
+                v += t * t;
+            }
+            red[q * BN + c] = v;
+            __syncthreads();
+            const double sd = n_g > 0 ? sqrt((((red[c] + red[BN + c]) + red[2 * BN + c]) + red[3 * BN + c]) / n_g) : 0.0;
+            const double rs = sd == 0.0 ? 1.0 : 1.0 / sd;
+            __syncthreads();
+            for (int r = lo[g] + q; r < hi[g]; r += 4) {
+                const double raw = T[r * LDT + c];
+                if (g == 2) out[(long)(EVAL_PAD + r - n_test) * Dp + d0 + c] = raw;   // *_no_std scores use the raw rows
+                out[(long)r * Dp + d0 + c] = (raw - mu) * rs;
+            }
+        }
+        // zero rows: n_eval .. EVAL_PAD-1 and EVAL_PAD + n_im .. YHAT_ROWS-1
+        for (int r = n_eval + q; r < YHAT_ROWS; r += 4)
+            if (r < EVAL_PAD || r >= EVAL_PAD + prm.n_im) out[(long)r * Dp + d0 + c] = 0.0;
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < 9; ++i) {
         const int row = wm * 72 + i * 8 + fr;
@@ -108,7 +158,7 @@ cudaError_t launch_predict(const PredictParams& p, cudaStream_t s) {
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    if (p.kp_max > 2048) return cudaErrorInvalidValue;
+    if (p.kp_max > 2048 || p.n_im > YHAT_ROWS - EVAL_PAD) return cudaErrorInvalidValue;
     dim3 grid(p.Dp / BN, p.n_tasks);
     predict_kernel<<<grid, THREADS, predict_smem_bytes(), s>>>(p);
     return cudaGetLastError();

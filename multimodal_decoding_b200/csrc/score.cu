@@ -1,13 +1,14 @@
-// The eight pairwise-accuracy scores of one searchlight centre, fused:
-//   per-feature z-scoring of each prediction group (eval.py:118, StandardScaler semantics, ddof = 0,
-//   zero-variance features keep scale 1) -> cosine distances to the candidate latents (eval.py:103-104)
-//   -> strict '<' comparison counts against each row's own candidate (eval.py:107-113)
+// The eight pairwise-accuracy scores of one searchlight centre:
+//   cosine distances between the (already z-scored, see predict.cu) predictions and the candidate latents
+//   (eval.py:103-104) -> strict '<' comparison counts against each row's own candidate (eval.py:107-113)
 //   -> count / (rows*cols - diag) for the metric table of SURVEY.md §3.2 (eval.py:126-181,
 //   searchlight.py:81-88).
 //
-// Row layout of yhat / candidates (set up by the host): [captions | images | imagery | zero pad].
-// One CTA per centre.  The (152 x 144) x Dp inner products run on the fp64 tensor pipe; rows
-// 144..146 of the product are the un-standardised imagery predictions (the *_no_std scores).
+// Row layout of yhat / candidates (set up by the host and predict.cu): [captions | images | imagery | zero pad],
+// rows 144..146 of yhat are the un-standardised imagery predictions (the *_no_std scores).
+// One CTA per centre.  The (152 x 144) x Dp inner products run on the fp64 tensor pipe in two passes of 80
+// rows; both operands are float64 in global memory and go through a 4-stage cp.async ring, so the loop has
+// the same shape as predict.cu's.  Row norms are accumulated from the staged tiles.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -17,56 +18,38 @@ constexpr int THREADS = 288;
 constexpr int KC = 16, LDS = KC + 4;
 constexpr int PASS_ROWS = 80;             // 10 m-tiles per pass, two passes cover 152 rows (19 tiles + 1 idle)
 constexpr int RAW_ROW0 = EVAL_PAD;        // first un-standardised imagery row
-constexpr int M_ROWS = EVAL_PAD + 8;
+constexpr int M_ROWS = YHAT_ROWS;
+constexpr int STAGES = 4;
+constexpr int A_STAGE = PASS_ROWS * LDS, B_STAGE = EVAL_PAD * LDS;   // doubles per stage
+constexpr int CHUNKS = (PASS_ROWS + EVAL_PAD) * (KC / 2);             // 16-byte copies per stage
+static_assert(M_ROWS <= 2 * PASS_ROWS && 2 * PASS_ROWS <= 5 * 32, "row-norm threads: two per row, warps 0-4");
 }  // namespace
 
-size_t score_smem_bytes(int Dp) {
-    return (size_t)6 * Dp * sizeof(double)                                   // mean / rstd for 3 groups
-           + (size_t)2 * (PASS_ROWS + EVAL_PAD) * LDS * sizeof(double)       // double-buffered A and B chunks
-           + (size_t)(3 * 160) * sizeof(double);                             // row norms, same/cross diagonals
+size_t score_smem_bytes(int) {
+    return (size_t)STAGES * (A_STAGE + B_STAGE) * sizeof(double) + (size_t)(3 * 160) * sizeof(double);
 }
 
 __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int Dp = prm.Dp;
-    double* mean_sm = reinterpret_cast<double*>(smem_raw);       // [3][Dp]
-    double* rstd_sm = mean_sm + 3 * Dp;                          // [3][Dp]
-    double* As = rstd_sm + 3 * Dp;                               // [2][PASS_ROWS][LDS]
-    double* Bs = As + 2 * PASS_ROWS * LDS;                       // [2][EVAL_PAD][LDS]
-    double* nrm_sm = Bs + 2 * EVAL_PAD * LDS;                    // [160]
+    double* As = reinterpret_cast<double*>(smem_raw);            // [STAGES][PASS_ROWS][LDS]
+    double* Bs = As + STAGES * A_STAGE;                          // [STAGES][EVAL_PAD][LDS]
+    double* nrm_sm = Bs + STAGES * B_STAGE;                      // [160]
     double* dsame_sm = nrm_sm + 160;                             // [160]
     double* dcross_sm = dsame_sm + 160;                          // [160]
     __shared__ int cnt_sm[8];
 
     const int task_id = blockIdx.x;
     const CentreTask task = prm.tasks[task_id];
-    const double* yhat = prm.yhat + (long)task_id * EVAL_PAD * Dp;
+    const double* yhat = prm.yhat + (long)task_id * YHAT_ROWS * Dp;
     const int n_cap = prm.n_cap, n_img = prm.n_img, n_im = prm.n_im;
     const int n_test = n_cap + n_img, n_eval = n_test + n_im;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     if (tid < 8) cnt_sm[tid] = 0;
     for (int i = tid; i < 160; i += THREADS) nrm_sm[i] = 0.0;
-
-    // ---- per-feature statistics of the three prediction groups ----
-    for (int d = tid; d < Dp; d += THREADS) {
-        const int lo[3] = {0, n_cap, n_test}, hi[3] = {n_cap, n_test, n_eval};
-#pragma unroll
-        for (int g = 0; g < 3; ++g) {
-            const int n = hi[g] - lo[g];
-            double s = 0.0;
-            for (int r = lo[g]; r < hi[g]; ++r) s += yhat[(long)r * Dp + d];
-            const double mu = n > 0 ? s / n : 0.0;
-            double v = 0.0;
-            for (int r = lo[g]; r < hi[g]; ++r) {
-                const double t = yhat[(long)r * Dp + d] - mu;
-                v += t * t;
-            }
-            const double sd = n > 0 ? sqrt(v / n) : 0.0;
-            mean_sm[g * Dp + d] = mu;
-            rstd_sm[g * Dp + d] = sd == 0.0 ? 1.0 : 1.0 / sd;
-        }
-    }
+    // rows of the second pass beyond YHAT_ROWS are never loaded: keep them finite
+    for (int i = tid; i < STAGES * A_STAGE; i += THREADS) As[i] = 0.0;
     __syncthreads();
 
     const int fr = lane >> 2, fk = lane & 3;
@@ -74,65 +57,24 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) cnt[q] = 0;
     const int min_ci = n_cap < n_img ? n_cap : n_img;
+    const int nk = Dp / KC;
 
     for (int pass = 0; pass < 2; ++pass) {
         const int row0 = pass * PASS_ROWS;
-        // staging map: 640 double2 of A per chunk (3 slots per thread), one 16-byte load of B per thread
-        int a_row[3], a_src[3], a_grp[3], a_col[3];
-        double a_sq[3] = {0.0, 0.0, 0.0};
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            const int idx = tid + i * THREADS;
-            const int r = idx / 8;
-            a_col[i] = (idx % 8) * 2;
-            a_row[i] = idx < PASS_ROWS * 8 ? r : -1;
-            const int gm = row0 + r;
-            int src = -1, grp = -1;
-            if (gm < n_eval) {
-                src = gm;
-                grp = gm < n_cap ? 0 : (gm < n_test ? 1 : 2);
-            } else if (gm >= RAW_ROW0 && gm < RAW_ROW0 + n_im) {
-                src = n_test + (gm - RAW_ROW0);
-            }
-            a_src[i] = src;
-            a_grp[i] = grp;
-        }
-        const int b_row = tid / 2, b_col = (tid % 2) * 8;
-
-        double2 a_reg[3];
-        uint4 b_reg;
-        auto fetch = [&](int kc) {
+        const int a_rows = min(PASS_ROWS, M_ROWS - row0);
+        auto load_stage = [&](int stage, int kc) {
             const int d0 = kc * KC;
-#pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                double2 v = make_double2(0.0, 0.0);
-                if (a_row[i] >= 0 && a_src[i] >= 0) {
-                    v = *reinterpret_cast<const double2*>(yhat + (long)a_src[i] * Dp + d0 + a_col[i]);
-                    if (a_grp[i] >= 0) {
-                        const double* mu = mean_sm + a_grp[i] * Dp + d0 + a_col[i];
-                        const double* rs = rstd_sm + a_grp[i] * Dp + d0 + a_col[i];
-                        v.x = (v.x - mu[0]) * rs[0];
-                        v.y = (v.y - mu[1]) * rs[1];
-                    }
+            double* as = As + stage * A_STAGE;
+            double* bs = Bs + stage * B_STAGE;
+            for (int c = tid; c < CHUNKS; c += THREADS) {
+                const int r = c / (KC / 2), cc = (c % (KC / 2)) * 2;
+                if (r < PASS_ROWS) {
+                    if (r < a_rows) cp_async16(as + r * LDS + cc, yhat + (long)(row0 + r) * Dp + d0 + cc);
+                } else {
+                    const int rb = r - PASS_ROWS;
+                    cp_async16(bs + rb * LDS + cc, prm.cand + (long)rb * Dp + d0 + cc);
                 }
-                a_reg[i] = v;
             }
-            b_reg = *reinterpret_cast<const uint4*>(prm.cand + (long)b_row * Dp + d0 + b_col);
-        };
-        auto stash = [&](int buf) {
-            double* as = As + buf * PASS_ROWS * LDS;
-            double* bs = Bs + buf * EVAL_PAD * LDS;
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-                if (a_row[i] >= 0) {
-                    *reinterpret_cast<double2*>(as + a_row[i] * LDS + a_col[i]) = a_reg[i];
-                    a_sq[i] += a_reg[i].x * a_reg[i].x + a_reg[i].y * a_reg[i].y;
-                }
-            const __half* h = reinterpret_cast<const __half*>(&b_reg);
-            double* dst = bs + b_row * LDS + b_col;
-#pragma unroll
-            for (int e = 0; e < 8; e += 2)
-                *reinterpret_cast<double2*>(dst + e) = make_double2(h2d(h[e]), h2d(h[e + 1]));
         };
 
         double acc[10][2][2];
@@ -140,15 +82,32 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
         for (int i = 0; i < 10; ++i)
 #pragma unroll
             for (int j = 0; j < 2; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        double sq = 0.0;                                  // threads 0..159: half a row of the squared norm
 
-        const int nk = Dp / KC;
-        fetch(0);
-        stash(0);
-        __syncthreads();
+        for (int s = 0; s < STAGES - 1; ++s) {
+            if (s < nk) load_stage(s, s);
+            cp_async_commit();
+        }
         for (int kc = 0; kc < nk; ++kc) {
-            if (kc + 1 < nk) fetch(kc + 1);
-            const double* as = As + (kc & 1) * PASS_ROWS * LDS + fr * LDS + fk;
-            const double* bs = Bs + (kc & 1) * EVAL_PAD * LDS + (warp * 16 + fr) * LDS + fk;
+            cp_async_wait<STAGES - 2>();
+            __syncthreads();
+            {
+                const int nxt = kc + STAGES - 1;
+                if (nxt < nk) load_stage(nxt % STAGES, nxt);
+                cp_async_commit();
+            }
+            const double* a_st = As + (kc % STAGES) * A_STAGE;
+            if (tid < 2 * PASS_ROWS) {
+                const double* x = a_st + (tid >> 1) * LDS + (tid & 1) * (KC / 2);
+#pragma unroll
+                for (int e = 0; e < KC / 2; e += 2) {
+                    const double2 v = *reinterpret_cast<const double2*>(x + e);
+                    sq = fma(v.x, v.x, sq);
+                    sq = fma(v.y, v.y, sq);
+                }
+            }
+            const double* as = a_st + fr * LDS + fk;
+            const double* bs = Bs + (kc % STAGES) * B_STAGE + (warp * 16 + fr) * LDS + fk;
 #pragma unroll
             for (int k4 = 0; k4 < KC / 4; ++k4) {
                 const double b0 = bs[k4 * 4], b1 = bs[8 * LDS + k4 * 4];
@@ -159,12 +118,12 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
                     dmma884(acc[i][1][0], acc[i][1][1], a, b1);
                 }
             }
-            if (kc + 1 < nk) stash((kc + 1) & 1);
-            __syncthreads();
         }
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-            if (a_row[i] >= 0) atomicAdd(&nrm_sm[row0 + a_row[i]], a_sq[i]);
+        cp_async_wait<0>();
+        if (tid < 2 * PASS_ROWS) {                         // warps 0-4, both halves of a row sit in adjacent lanes
+            sq += __shfl_xor_sync(0xffffffffu, sq, 1);
+            if ((tid & 1) == 0) nrm_sm[row0 + (tid >> 1)] = sq;
+        }
         __syncthreads();
 
         // ---- distances; first publish each row's own ("same") and cross-modal diagonal entries ----
@@ -247,7 +206,8 @@ cudaError_t launch_score(const ScoreParams& p, cudaStream_t s) {
     const size_t smem = score_smem_bytes(p.Dp);
     cudaError_t e = cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    if (p.n_cap + p.n_img + p.n_im > EVAL_PAD - 1 || p.n_im > 8) return cudaErrorInvalidValue;
+    if (p.n_cap + p.n_img + p.n_im > EVAL_PAD - 1 || p.n_im > YHAT_ROWS - EVAL_PAD || p.Dp % KC != 0)
+        return cudaErrorInvalidValue;
     score_kernel<<<p.n_tasks, THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
