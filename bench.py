@@ -47,7 +47,7 @@ def parse_args():
     p.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                    help="weak: every GPU runs one whole hemisphere job per step (configs[4] distributes whole "
                         "searchlights); strong: ONE hemisphere, centres sharded across the GPUs")
-    p.add_argument("--cpu-centres", type=int, default=256, help="centres of the CPU-baseline sample")
+    p.add_argument("--cpu-centres", type=int, default=1024, help="centres of the CPU-baseline sample")
     p.add_argument("--batch-centres", type=int, default=0, help="engine knob: centres per kernel batch (0 = default)")
     p.add_argument("--cluster-size", type=int, default=0, help="engine knob: centres per union-Gram cluster (0 = default)")
     p.add_argument("--no-cpu-baseline", action="store_true")
@@ -198,6 +198,9 @@ def cpu_centres_per_sec(X, Y, A_rows, ids, n_centres, budget_s=30.0):
 # ----------------------------------------------------------------------------------------------------------
 # roofline bookkeeping
 # ----------------------------------------------------------------------------------------------------------
+# DRAM bytes per centre (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of a full batch,
+# divided by the batch's centres): profiles/r1_*_v2_details.csv, captured with tools/gpu_round.sh at config 2.
+NCU_DRAM_BYTES_PER_CENTRE = {"factor_solve": 41.5e6, "predict": 2.18e6, "score": 1.27e6, "syrk": 0.08e6}
 FP64_TENSOR_PEAK_TFLOPS = 37.1      # DMMA m8n8k4, measured on this pool with tools/peak_probe.cu (gpurun_out_peaks.log)
 
 
@@ -231,12 +234,19 @@ def roofline_entry(stats, n_centres, args, peaks):
     k, ntr, D = args.n_neighbors, args.n_train, args.n_dims
     t = ms[top] * 1e-3
     shares = {s: round(ms[s] / max(sum(ms[x] for x in per_centre), 1e-9), 4) for s in per_centre}
-    out = {"kernel": top, "stage_ms": {s: round(ms[s], 3) for s in per_centre}, "stage_share": shares}
+    n_batches = max(stats["launches"] // len(per_centre), 1)         # every batch launches each per-centre kernel once
+    config2 = (k, ntr, D) == (750, 4000, 1024)
+    traffic = (round(NCU_DRAM_BYTES_PER_CENTRE[top] * n_centres / n_batches) if config2 and top in NCU_DRAM_BYTES_PER_CENTRE
+               else None)
+    out = {"kernel": top, "stage_ms": {s: round(ms[s], 3) for s in per_centre}, "stage_share": shares,
+           "launches_of_kernel": n_batches, "avg_launch_ms": round(ms[top] / n_batches, 3),
+           "traffic_source": "ncu --set full of one full batch, bytes per centre x centres per launch "
+                             "(profiles/r1_*_v2_details.csv)" if traffic else None}
     if top in ("syrk", "factor_solve", "predict"):
         executed = stats["syrk_flops"] if top == "syrk" else stage_flops_per_centre(top, k, ntr, 144, D) * n_centres
         achieved = executed / t / 1e12
         out.update({"bound": "tensor", "achieved": round(achieved, 3), "peak": FP64_TENSOR_PEAK_TFLOPS,
-                    "unit": "TFLOP/s", "frac": round(achieved / FP64_TENSOR_PEAK_TFLOPS, 4), "traffic": None,
+                    "unit": "TFLOP/s", "frac": round(achieved / FP64_TENSOR_PEAK_TFLOPS, 4), "traffic": traffic,
                     "peak_source": "fp64 tensor pipe (DMMA) measured with tools/peak_probe.cu on this pool; "
                                    "MEASURED_PEAKS.json holds no fp64 figure",
                     "frac_of_bf16_peak": round(achieved / peaks["bf16_tflops"], 5),
@@ -245,10 +255,10 @@ def roofline_entry(stats, n_centres, args, peaks):
             out["algorithmic_equiv_tflops"] = round(2.0 * ntr * k * k * n_centres / t / 1e12, 2)
     else:
         n_eval = 143
-        bytes_alg = n_centres * (144.0 * ((D + 63) // 64 * 64) * 8 + 64) if top == "score" else n_centres * k * 8.0
+        bytes_alg = n_centres * (152.0 * ((D + 63) // 64 * 64) * 8 + 64) if top == "score" else n_centres * k * 8.0
         achieved = bytes_alg / t / 1e9
         out.update({"bound": "hbm", "achieved": round(achieved, 2), "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                    "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": None,
+                    "frac": round(achieved / peaks["hbm_gbs"], 4), "traffic": traffic,
                     "peak_source": peaks["source"]})
     return out
 
@@ -435,12 +445,13 @@ def run_reference(args):
     from oracle import searchlight_oracle as orc
     k, n_tr, D = args.n_neighbors, args.n_train, args.n_dims
     cores = host_cores()
-    n_c = 2 * cores                                             # centres per step (bounded sample)
+    n_c = 8 * cores                                             # centres per step (bounded sample)
     mesh = syn.make_mesh(level=args.mesh_level, seed=7)
     rng = np.random.default_rng(0)
     # the neighbourhood columns of the sampled centres only: same shapes/dtypes as the GPU arm's workload
     c64 = mesh.coords.astype(np.float64)
-    centres = np.arange((args.warmup + args.steps) * n_c)
+    d0 = c64 - c64[0]                                           # a compact patch of cortex, like a GPU cluster
+    centres = np.argsort((d0[:, 0] ** 2 + d0[:, 1] ** 2) + d0[:, 2] ** 2, kind="stable")[:(args.warmup + args.steps) * n_c]
     nbrs = []
     for c in centres:
         d = c64 - c64[c]

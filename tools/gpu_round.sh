@@ -8,14 +8,14 @@ timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo 
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2>&1
 timeout 900 python bench.py > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/bench.log
 SMALL="--centres-per-step 4096 --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
-KREG='regex:(factor_solve|predict_kernel|score_kernel|gemm_nt|prep_tasks|pack_transpose|knn_kernel)'
+KREG='regex:(factor_solve|predict_kernel|score_kernel|gemm_nt|prep_tasks|pack_transpose|knn_kernel|radius_kernel|half_to_double|row_sqnorm|gather_rows)'
 timeout 600 python bench.py $SMALL > gpurun_out/bench_small.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" -c 400 --csv \
    --log-file gpurun_out/launches.csv python bench.py $SMALL > gpurun_out/ncu_launches.log 2>&1
 for kn in factor_solve_kernel predict_kernel score_kernel; do
-  timeout 900 ncu --set full --clock-control none --import-source on -k $kn -s 2 -c 1 -f -o gpurun_out/${kn} \
+  timeout 900 ncu --set full --clock-control none --import-source on -k $kn -s 0 -c 1 -f -o gpurun_out/${kn} \
      python bench.py $SMALL > gpurun_out/ncu_${kn}.log 2>&1
 done
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_nt -s 3 -c 1 -f -o gpurun_out/gemm_syrk \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_nt -s 1 -c 1 -f -o gpurun_out/gemm_syrk \
      python bench.py $SMALL > gpurun_out/ncu_gemm.log 2>&1
 ls -la gpurun_out
