@@ -50,6 +50,7 @@ def parse_args():
     p.add_argument("--cpu-centres", type=int, default=1024, help="centres of the CPU-baseline sample")
     p.add_argument("--batch-centres", type=int, default=0, help="engine knob: centres per kernel batch (0 = default)")
     p.add_argument("--cluster-size", type=int, default=0, help="engine knob: centres per union-Gram cluster (0 = default)")
+    p.add_argument("--group-size", type=int, default=0, help="engine knob: centres per prefix-sharing group (1 = off, 0 = default)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     return p.parse_args()
@@ -234,7 +235,7 @@ def roofline_entry(stats, n_centres, args, peaks):
     k, ntr, D = args.n_neighbors, args.n_train, args.n_dims
     t = ms[top] * 1e-3
     shares = {s: round(ms[s] / max(sum(ms[x] for x in per_centre), 1e-9), 4) for s in per_centre}
-    n_batches = max(stats["launches"] // len(per_centre), 1)         # every batch launches each per-centre kernel once
+    n_batches = max(stats["batches"], 1)                             # every batch launches each per-centre kernel once
     config2 = (k, ntr, D) == (750, 4000, 1024)
     traffic = (round(NCU_DRAM_BYTES_PER_CENTRE[top] * n_centres / n_batches) if config2 and top in NCU_DRAM_BYTES_PER_CENTRE
                else None)
@@ -243,7 +244,8 @@ def roofline_entry(stats, n_centres, args, peaks):
            "traffic_source": "ncu --set full of one full batch, bytes per centre x centres per launch "
                              "(profiles/r1_*_v2_details.csv)" if traffic else None}
     if top in ("syrk", "factor_solve", "predict"):
-        executed = stats["syrk_flops"] if top == "syrk" else stage_flops_per_centre(top, k, ntr, 144, D) * n_centres
+        executed = (stats["syrk_flops"] if top == "syrk" else stats["solve_flops"] if top == "factor_solve"
+                    else stage_flops_per_centre(top, k, ntr, 144, D) * n_centres)
         achieved = executed / t / 1e12
         out.update({"bound": "tensor", "achieved": round(achieved, 3), "peak": FP64_TENSOR_PEAK_TFLOPS,
                     "unit": "TFLOP/s", "frac": round(achieved / FP64_TENSOR_PEAK_TFLOPS, 4), "traffic": traffic,
@@ -251,6 +253,13 @@ def roofline_entry(stats, n_centres, args, peaks):
                                    "MEASURED_PEAKS.json holds no fp64 figure",
                     "frac_of_bf16_peak": round(achieved / peaks["bf16_tflops"], 5),
                     "flops": "executed float64 flops (<= the reference's algorithmic count)"})
+        if top == "factor_solve":
+            full = stage_flops_per_centre(top, k, ntr, 144, D) * n_centres
+            out["prefix_sharing"] = {
+                "grouped_centres_frac": round(stats["grouped_centres"] / max(n_centres, 1), 4),
+                "mean_shared_prefix": round(stats["sum_shared_prefix"] / max(stats["grouped_centres"], 1), 1),
+                "shared_core_factorisations": int(stats["core_tasks"]),
+                "executed_over_unshared_flops": round(executed / full, 4)}
         if top == "syrk":
             out["algorithmic_equiv_tflops"] = round(2.0 * ntr * k * k * n_centres / t / 1e12, 2)
     else:
@@ -299,8 +308,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     eng = sl.get_engine(local)
-    if args.batch_centres or args.cluster_size:
-        eng.configure(cluster_size=args.cluster_size, batch_centres=args.batch_centres)
+    if args.batch_centres or args.cluster_size or args.group_size:
+        eng.configure(cluster_size=args.cluster_size, batch_centres=args.batch_centres, group_size=args.group_size)
     stream = torch.cuda.ExternalStream(eng.stream_ptr, device=device)
     K, W, cps, k = args.steps, args.warmup, args.centres_per_step, args.n_neighbors
 
@@ -429,6 +438,8 @@ def run_ours(args):
                       "upload_stage_ms": {s: round(v, 2) for s, v in upload_stats["stage_ms"].items() if v > 0},
                       "total_s": round(setup_s, 1)},
             "clusters_per_step": stats["clusters"] / K,
+            "host_ms_per_step": {"plan": round(stats["host_plan_ms"] / K, 1),
+                                 "adjacency_h2d": round(stats["host_adjacency_h2d_ms"] / K, 1)},
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -129,6 +129,18 @@ int mmd_get_stats(mmd_handle* h, float stage_ms[MMD_N_STAGES], int64_t* n_launch
 void mmd_reset_stats(mmd_handle* h);
 const char* mmd_stage_name(int i);
 
+/* More counters since the last mmd_reset_stats: [0] batches (every batch launches each per-centre kernel once),
+ * [1] shared-core factorisations, [2] centres that used a shared core, [3] sum of their shared prefix lengths,
+ * [4] host microseconds spent grouping centres (clusters, unions, shared cores), [5] host microseconds to hand the
+ * adjacency to the device;
+ * solve_flops = float64 flops executed by the factorisation / triangular-solve stage. */
+#define MMD_N_COUNTERS 6
+int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* solve_flops);
+
+/* Prefix sharing: up to `group_size` neighbouring centres factor the part of their normal matrices that belongs to
+ * the neighbours they all share only once (1 = off; default 6).  The scores do not depend on it. */
+int mmd_set_group_size(mmd_handle* h, int group_size);
+
 /* Tuning knobs (0 keeps the default): centres per cluster, max centres per batch. */
 int mmd_configure(mmd_handle* h, int cluster_size, int batch_centres, int host_threads);
 

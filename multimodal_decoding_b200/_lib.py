@@ -13,7 +13,7 @@ EVAL_PAD = 144
 
 EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload",
-    "mmd_searchlight", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
+    "mmd_searchlight", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
 ]
 
@@ -66,6 +66,10 @@ def load():
     lib.mmd_predict_centre.restype = i32
     lib.mmd_get_stats.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i64), C.POINTER(i64), C.POINTER(dbl)]
     lib.mmd_get_stats.restype = i32
+    lib.mmd_get_counters.argtypes = [vp, C.POINTER(i64), C.POINTER(dbl)]
+    lib.mmd_get_counters.restype = i32
+    lib.mmd_set_group_size.argtypes = [vp, i32]
+    lib.mmd_set_group_size.restype = i32
     lib.mmd_reset_stats.argtypes = [vp]
     lib.mmd_reset_stats.restype = None
     lib.mmd_configure.argtypes = [vp, i32, i32, i32]

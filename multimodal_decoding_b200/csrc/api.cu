@@ -7,6 +7,7 @@
 // cuts the Gram work per centre from 2*N*k^2 to ~2*N*u^2/(2*128) (reported as executed flops).
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -72,18 +73,19 @@ struct mmd_handle {
     bool uploaded = false;
     DevBuf Xt, Xe, Yt, cand, cand64, cand_sq, XtY;
     // per-call / per-batch workspaces
-    DevBuf adj, union_vertices, task_row, task_k, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
+    DevBuf adj, union_vertices, task_row, task_k, task_core_off, task_core_n, core_work, group_flags, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
     DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
     int n_perm = 0;
     std::vector<int> int_of_test;   // position in test_ids order -> internal evaluation row (captions first)
     // knobs
-    int cluster_size = 256, batch_centres = 2048, host_threads = 0;
+    int cluster_size = 256, batch_centres = 2048, host_threads = 0, group_size = 6;
     // stats
     float stage_ms[MMD_N_STAGES] = {0};
-    int64_t launches = 0, n_clusters = 0;
-    double syrk_flops = 0.0;
+    int64_t launches = 0, n_clusters = 0, n_batches = 0, n_core_tasks = 0, n_grouped = 0, sum_sp = 0, plan_us = 0,
+            adj_h2d_us = 0;
+    double syrk_flops = 0.0, solve_flops = 0.0;
     std::vector<cudaEvent_t> event_pool;
     size_t events_used = 0;
     std::vector<TimedSpan> spans;
@@ -160,6 +162,12 @@ struct Plan {
     std::vector<int> members;     // centre (adjacency row) indices
     std::vector<long> un_off;     // union of cluster c = un_vert[un_off[c] .. un_off[c+1])
     std::vector<int> un_vert;     // ascending vertex ids
+    // prefix-sharing groups: nearby centres of one cluster whose neighbourhoods share a core of s_p vertices
+    std::vector<int> cl_grp_off;  // cluster c owns groups [cl_grp_off[c], cl_grp_off[c+1])
+    std::vector<int> grp_off;     // group g owns members[grp_off[g] .. grp_off[g+1]) (groups never straddle clusters)
+    std::vector<int> grp_sp;      // shared prefix length of group g: multiple of 64, 0 = none
+    std::vector<long> core_off;   // core of group g = core_vert[core_off[g] .. + grp_sp[g]), ascending vertex ids
+    std::vector<int> core_vert;
 };
 
 // Neighbourhood lists of one call: rectangular (n x k, the k-NN branch of get_adjacency_matrix,
@@ -177,7 +185,9 @@ struct Rows {
     long total() const { return off ? (long)off[n] : (long)n * k; }
 };
 
-void build_plan(const Rows& rows, int V, int cluster_size, int n_threads, Plan& plan) {
+constexpr int MIN_SHARED_PREFIX = 128;
+
+void build_plan(const Rows& rows, int V, int cluster_size, int group_size, int n_threads, Plan& plan) {
     // greedy region growing: a seed takes its nearest still-unassigned centres (k-NN adjacency rows are ordered
     // by distance in the reference, the centre itself first; radius rows are in vertex order and scanned whole)
     const int n_centres = rows.n;
@@ -210,15 +220,81 @@ void build_plan(const Rows& rows, int V, int cluster_size, int n_threads, Plan& 
         plan.cl_off.push_back((int)plan.members.size());
     }
     const int n_clusters = (int)plan.cl_off.size() - 1;
-    // unions, in parallel over clusters
+    // unions and prefix-sharing groups, in parallel over clusters
+    struct ClusterGroups {
+        std::vector<int> order;       // the cluster's members, groups contiguous
+        std::vector<int> size, sp;    // per group
+        std::vector<int> core;        // concatenated cores (sp entries each)
+    };
     std::vector<std::vector<int>> unions(n_clusters);
+    std::vector<ClusterGroups> cgroups(n_clusters);
+    const bool grouping = !rows.off && group_size >= 2 && rows.k > MIN_SHARED_PREFIX;
     n_threads = std::max(1, std::min(n_threads, n_clusters));
     std::atomic<int> next(0);
     auto worker = [&]() {
         std::vector<int> stamp(V, -1);
+        std::vector<int> member_of, grouped, vgen, vcnt;
+        if (grouping) {
+            member_of.assign(n_centres, -1);
+            grouped.assign(n_centres, 0);
+            vgen.assign(V, -1);
+            vcnt.assign(V, 0);
+        }
+        int gen = 0;
         for (;;) {
             const int c = next.fetch_add(1);
             if (c >= n_clusters) break;
+            if (grouping) {
+                // Greedy groups: a seed takes its nearest not yet grouped centres of the same cluster; the core is the
+                // intersection of the members' neighbourhoods, cut to a multiple of 64 (any subset may be shared).
+                ClusterGroups& cg = cgroups[c];
+                for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) member_of[plan.members[m]] = c;
+                const int kp = round_up(rows.k, NB);
+                for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) {
+                    const int s0 = plan.members[m];
+                    if (grouped[s0]) continue;
+                    grouped[s0] = 1;
+                    const size_t first = cg.order.size();
+                    cg.order.push_back(s0);
+                    const int32_t* row = rows.row(s0);
+                    const int scan = std::min(rows.k, 4 * group_size);
+                    for (int j = 1; j < scan && (int)(cg.order.size() - first) < group_size; ++j) {
+                        const int v = row[j];
+                        if (v < 0 || v >= V) continue;
+                        const int cc = centre_of[v];
+                        if (cc >= 0 && member_of[cc] == c && !grouped[cc] && rows.anchor(cc) == v) {
+                            grouped[cc] = 1;
+                            cg.order.push_back(cc);
+                        }
+                    }
+                    const int g = (int)(cg.order.size() - first);
+                    int sp = 0;
+                    if (g >= 2) {
+                        ++gen;
+                        for (int q = 0; q < g; ++q) {
+                            const int32_t* r = rows.row(cg.order[first + q]);
+                            for (int j = 0; j < rows.k; ++j) {
+                                const int v = r[j];
+                                if (v < 0 || v >= V) continue;
+                                if (vgen[v] != gen) { vgen[v] = gen; vcnt[v] = 1; }
+                                else ++vcnt[v];
+                            }
+                        }
+                        const size_t core0 = cg.core.size();
+                        for (int j = 0; j < rows.k; ++j) {
+                            const int v = row[j];
+                            if (v >= 0 && v < V && vgen[v] == gen && vcnt[v] == g) { cg.core.push_back(v); vcnt[v] = -1; }
+                        }
+                        const int n_core = (int)(cg.core.size() - core0);
+                        sp = std::min(n_core / NB * NB, kp - NB);
+                        if (sp < MIN_SHARED_PREFIX) sp = 0;
+                        std::sort(cg.core.begin() + core0, cg.core.end());
+                        cg.core.resize(core0 + sp);
+                    }
+                    cg.size.push_back(g);
+                    cg.sp.push_back(sp);
+                }
+            }
             std::vector<int>& u = unions[c];
             for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) {
                 const int32_t* row = rows.row(plan.members[m]);
@@ -248,6 +324,31 @@ void build_plan(const Rows& rows, int V, int cluster_size, int n_threads, Plan& 
         plan.un_vert.insert(plan.un_vert.end(), u.begin(), u.end());
         plan.un_off.push_back((long)plan.un_vert.size());
     }
+    // groups: reorder the members of every cluster so that groups are contiguous
+    plan.cl_grp_off.assign(1, 0);
+    plan.grp_off.assign(1, 0);
+    plan.grp_sp.clear();
+    plan.core_off.clear();
+    plan.core_vert.clear();
+    for (int c = 0; c < n_clusters; ++c) {
+        if (grouping) {
+            const ClusterGroups& cg = cgroups[c];
+            std::copy(cg.order.begin(), cg.order.end(), plan.members.begin() + plan.cl_off[c]);
+            size_t core_pos = 0;
+            for (size_t g = 0; g < cg.size.size(); ++g) {
+                plan.grp_off.push_back(plan.grp_off.back() + cg.size[g]);
+                plan.grp_sp.push_back(cg.sp[g]);
+                plan.core_off.push_back((long)plan.core_vert.size());
+                plan.core_vert.insert(plan.core_vert.end(), cg.core.begin() + core_pos, cg.core.begin() + core_pos + cg.sp[g]);
+                core_pos += cg.sp[g];
+            }
+        } else {
+            plan.grp_off.push_back(plan.cl_off[c + 1]);          // one group without a shared prefix
+            plan.grp_sp.push_back(0);
+            plan.core_off.push_back((long)plan.core_vert.size());
+        }
+        plan.cl_grp_off.push_back((int)plan.grp_sp.size());
+    }
 }
 
 int run_xty(mmd_handle* h) {
@@ -272,16 +373,22 @@ int run_xty(mmd_handle* h) {
 }
 
 // One batch = clusters [c0, c1).  `slot0` = first output slot when yhat_only (diagnostic) is set.
-int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1, int k_max, int kp, double alpha,
-              bool with_null, bool raw_yhat) {
+int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1, int k_max, int kp, int sp_max,
+              double alpha, bool with_null, bool raw_yhat) {
     const int n_cl = c1 - c0;
     const int t0 = plan.cl_off[c0], n_tasks = plan.cl_off[c1] - t0;
-    std::vector<int> task_k(n_tasks), task_un_n(n_tasks);
-    std::vector<long> task_row_off(n_tasks), task_un_off(n_tasks);
-    std::vector<CentreTask> tasks(n_tasks);
+    // core tasks (one per group with a shared prefix) follow the centre tasks in every per-task array
+    int n_core = 0;
+    for (int g = plan.cl_grp_off[c0]; g < plan.cl_grp_off[c1]; ++g) n_core += plan.grp_sp[g] > 0;
+    const int n_all = n_tasks + n_core;
+    const long adj_total = rows.total();                    // the cores sit behind the adjacency rows on the device
+    const size_t core_stride = (size_t)(sp_max + EVAL_PAD) * sp_max;
+    std::vector<int> task_k(n_all), task_un_n(n_all), task_core_n(n_all, 0);
+    std::vector<long> task_row_off(n_all), task_un_off(n_all), task_core_off(n_all, 0);
+    std::vector<CentreTask> tasks(n_all);
     std::vector<GemmProblem> probs(n_cl);
     size_t pool_doubles = 0;
-    int max_u = 0;
+    int max_u = 0, q = 0;
     for (int c = c0; c < c1; ++c) {
         const int u = (int)(plan.un_off[c + 1] - plan.un_off[c]);
         const long ldu = round_up(u, 8);
@@ -294,20 +401,54 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
         p.C = h->gram_pool.as<double>() + pool_doubles;     // pool base fixed before this call
         p.ldc = ldu;
         p.lower_only = 1;
-        for (int m = plan.cl_off[c]; m < plan.cl_off[c + 1]; ++m) {
-            const int t = m - t0;
-            task_row_off[t] = rows.row_off(plan.members[m]);
-            task_k[t] = rows.len(plan.members[m]);
-            task_un_off[t] = plan.un_off[c];
-            task_un_n[t] = u;
-            CentreTask& ct = tasks[t];
-            ct.gram = p.C;
-            ct.gram_ld = ldu;
-            ct.loc = h->loc.as<int>() + (long)t * kp;
-            ct.nbr = h->nbr_sorted.as<int>() + (long)t * kp;
-            ct.centre = plan.members[m];
-            ct.k = task_k[t];
-            ct.kp = round_up(task_k[t], NB);
+        for (int g = plan.cl_grp_off[c]; g < plan.cl_grp_off[c + 1]; ++g) {
+            const int sp = plan.grp_sp[g];
+            const double* core_work = nullptr;
+            const int* core_flag = nullptr;
+            if (sp > 0) {
+                const int t = n_tasks + q;
+                task_row_off[t] = adj_total + plan.core_off[g];
+                task_k[t] = sp;
+                task_un_off[t] = plan.un_off[c];
+                task_un_n[t] = u;
+                CentreTask& ct = tasks[t];
+                ct.gram = p.C;
+                ct.gram_ld = ldu;
+                ct.loc = h->loc.as<int>() + (long)t * kp;
+                ct.nbr = h->nbr_sorted.as<int>() + (long)t * kp;
+                ct.centre = q;
+                ct.k = ct.kp = sp;
+                ct.s_p = 0;
+                ct.core_work = nullptr;
+                ct.core_flag = nullptr;
+                core_work = h->core_work.as<double>() + (size_t)q * core_stride;
+                core_flag = h->group_flags.as<int>() + q;
+                h->solve_flops += (double)sp * sp * sp / 3.0 + (double)EVAL_PAD * sp * sp;
+                ++q;
+            }
+            for (int m = plan.grp_off[g]; m < plan.grp_off[g + 1]; ++m) {
+                const int t = m - t0;
+                task_row_off[t] = rows.row_off(plan.members[m]);
+                task_k[t] = rows.len(plan.members[m]);
+                task_un_off[t] = plan.un_off[c];
+                task_un_n[t] = u;
+                task_core_off[t] = adj_total + plan.core_off[g];
+                task_core_n[t] = sp;
+                CentreTask& ct = tasks[t];
+                ct.gram = p.C;
+                ct.gram_ld = ldu;
+                ct.loc = h->loc.as<int>() + (long)t * kp;
+                ct.nbr = h->nbr_sorted.as<int>() + (long)t * kp;
+                ct.centre = plan.members[m];
+                ct.k = task_k[t];
+                ct.kp = round_up(task_k[t], NB);
+                ct.s_p = sp;
+                ct.core_work = core_work;
+                ct.core_flag = core_flag;
+                const double kpd = ct.kp, spd = sp;
+                h->solve_flops += (kpd * kpd * kpd - spd * spd * spd) / 3.0 + EVAL_PAD * (kpd * kpd - spd * spd) +
+                                  EVAL_PAD * kpd * kpd;
+            }
         }
         pool_doubles += (size_t)u * ldu;
         max_u = std::max(max_u, u);
@@ -317,18 +458,23 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
         for (long i = 0; i < tm; ++i) tiles += std::min<long>((i * 128 + 127) / 64 + 1, (u + 63) / 64);
         h->syrk_flops += 2.0 * tiles * 128.0 * 64.0 * h->ldt;
     }
+    h->n_batches += 1;
+    h->n_core_tasks += n_core;
     if (pool_doubles * sizeof(double) > h->gram_pool.bytes) return fail(h, "internal: gram pool too small");
-    if (to_device(h, h->task_row, task_row_off.data(), n_tasks)) return 1;
-    if (to_device(h, h->task_k, task_k.data(), n_tasks)) return 1;
-    if (to_device(h, h->task_union_off, task_un_off.data(), n_tasks)) return 1;
-    if (to_device(h, h->task_union_n, task_un_n.data(), n_tasks)) return 1;
-    if (to_device(h, h->tasks, tasks.data(), n_tasks)) return 1;
+    if (to_device(h, h->task_row, task_row_off.data(), n_all)) return 1;
+    if (to_device(h, h->task_k, task_k.data(), n_all)) return 1;
+    if (to_device(h, h->task_union_off, task_un_off.data(), n_all)) return 1;
+    if (to_device(h, h->task_union_n, task_un_n.data(), n_all)) return 1;
+    if (to_device(h, h->task_core_off, task_core_off.data(), n_all)) return 1;
+    if (to_device(h, h->task_core_n, task_core_n.data(), n_all)) return 1;
+    if (to_device(h, h->tasks, tasks.data(), n_all)) return 1;
     if (to_device(h, h->probs, probs.data(), n_cl)) return 1;
 
     span_begin(h, ST_PREP);
     CU(launch_prep_tasks(h->adj.as<int>(), h->task_row.as<long>(), h->task_k.as<int>(), k_max, kp,
-                         h->task_union_off.as<long>(), h->task_union_n.as<int>(), h->union_vertices.as<int>(), h->V,
-                         n_tasks, h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
+                         h->task_union_off.as<long>(), h->task_union_n.as<int>(), h->union_vertices.as<int>(),
+                         h->task_core_off.as<long>(), h->task_core_n.as<int>(), h->V,
+                         n_all, h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
     span_end(h);
 
     span_begin(h, ST_SYRK);
@@ -343,9 +489,21 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     sp.Xe = h->Xe.as<__half>();
     sp.work = h->work.as<double>();
     sp.flags = h->flags.as<int>();
+    sp.core_only = 0;
     span_begin(h, ST_SOLVE);
+    if (n_core > 0) {
+        SolveParams cp = sp;                                   // the shared cores first: factorisation + forward solve
+        cp.tasks = sp.tasks + n_tasks;
+        cp.n_tasks = n_core;
+        cp.kp_max = sp_max;
+        cp.work = h->core_work.as<double>();
+        cp.flags = h->group_flags.as<int>();
+        cp.core_only = 1;
+        CU(cudaMemsetAsync(h->group_flags.p, 0, (size_t)n_core * sizeof(int), h->stream));
+        CU(launch_factor_solve(cp, h->stream));
+    }
     CU(launch_factor_solve(sp, h->stream));
-    span_end(h);
+    span_end(h, n_core > 0 ? 2 : 1);
 
     PredictParams pp{};
     pp.tasks = sp.tasks;
@@ -415,9 +573,26 @@ int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_nul
     int n_threads = h->host_threads > 0 ? h->host_threads : (int)std::thread::hardware_concurrency();
     n_threads = std::max(1, std::min(n_threads, 32));
 
-    if (to_device(h, h->adj, rows.data, (size_t)rows.total())) return 1;
     Plan plan;
-    build_plan(rows, h->V, h->cluster_size, n_threads, plan);
+    const auto t_plan0 = std::chrono::steady_clock::now();
+    build_plan(rows, h->V, h->cluster_size, h->group_size, n_threads, plan);
+    const auto t_plan1 = std::chrono::steady_clock::now();
+    h->plan_us += std::chrono::duration_cast<std::chrono::microseconds>(t_plan1 - t_plan0).count();
+    // adjacency rows, then the groups' shared cores (read by the prep kernel like rows)
+    CU(h->adj.ensure(((size_t)rows.total() + plan.core_vert.size() + 1) * sizeof(int)));
+    CU(cudaMemcpyAsync(h->adj.p, rows.data, (size_t)rows.total() * sizeof(int), cudaMemcpyDefault, h->stream));
+    if (!plan.core_vert.empty())
+        CU(cudaMemcpyAsync(h->adj.as<int>() + rows.total(), plan.core_vert.data(), plan.core_vert.size() * sizeof(int),
+                           cudaMemcpyDefault, h->stream));
+    h->adj_h2d_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_plan1).count();
+    int sp_max = 0;
+    for (size_t g = 0; g < plan.grp_sp.size(); ++g) {
+        sp_max = std::max(sp_max, plan.grp_sp[g]);
+        if (plan.grp_sp[g] > 0) {
+            h->n_grouped += plan.grp_off[g + 1] - plan.grp_off[g];
+            h->sum_sp += (int64_t)plan.grp_sp[g] * (plan.grp_off[g + 1] - plan.grp_off[g]);
+        }
+    }
     const int n_clusters = (int)plan.cl_off.size() - 1;
     h->n_clusters += n_clusters;
     if (to_device(h, h->union_vertices, plan.un_vert.data(), plan.un_vert.size())) return 1;
@@ -425,18 +600,23 @@ int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_nul
     // batches: whole clusters, at most batch_centres centres
     std::vector<int> batch_start(1, 0);
     size_t max_pool = 0, cur_pool = 0;
-    int cur_tasks = 0, max_tasks = 0;
+    int cur_tasks = 0, max_tasks = 0, cur_core = 0, max_core = 0;
     for (int c = 0; c < n_clusters; ++c) {
         const int m = plan.cl_off[c + 1] - plan.cl_off[c];
+        int n_core_c = 0;
+        for (int g = plan.cl_grp_off[c]; g < plan.cl_grp_off[c + 1]; ++g) n_core_c += plan.grp_sp[g] > 0;
         const size_t u = (size_t)(plan.un_off[c + 1] - plan.un_off[c]);
         const size_t g = u * round_up((int)u, 8);
         if (cur_tasks > 0 && cur_tasks + m > h->batch_centres) {
             batch_start.push_back(c);
             cur_tasks = 0;
             cur_pool = 0;
+            cur_core = 0;
         }
         cur_tasks += m;
         cur_pool += g;
+        cur_core += n_core_c;
+        max_core = std::max(max_core, cur_core);
         max_tasks = std::max(max_tasks, cur_tasks);
         max_pool = std::max(max_pool, cur_pool);
     }
@@ -445,8 +625,10 @@ int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_nul
     CU(h->gram_pool.ensure(max_pool * sizeof(double)));
     CU(h->work.ensure((size_t)max_tasks * (kp + EVAL_PAD) * kp * sizeof(double)));
     CU(h->yhat.ensure((size_t)max_tasks * YHAT_ROWS * h->Dp * sizeof(double)));
-    CU(h->nbr_sorted.ensure((size_t)max_tasks * kp * sizeof(int)));
-    CU(h->loc.ensure((size_t)max_tasks * kp * sizeof(int)));
+    CU(h->nbr_sorted.ensure((size_t)(max_tasks + max_core) * kp * sizeof(int)));
+    CU(h->loc.ensure((size_t)(max_tasks + max_core) * kp * sizeof(int)));
+    CU(h->core_work.ensure(std::max<size_t>((size_t)max_core * (sp_max + EVAL_PAD) * sp_max, 1) * sizeof(double)));
+    CU(h->group_flags.ensure(std::max<size_t>(max_core, 1) * sizeof(int)));
     CU(h->scores.ensure((size_t)n_centres * MMD_N_SCORES * sizeof(double)));
     CU(h->flags.ensure((size_t)n_centres * sizeof(int)));
     CU(h->misc_flag.ensure(sizeof(int)));
@@ -458,7 +640,7 @@ int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_nul
     }
 
     for (size_t b = 0; b + 1 < batch_start.size(); ++b)
-        if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, alpha, with_null, raw_yhat)) return 1;
+        if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, sp_max, alpha, with_null, raw_yhat)) return 1;
     return 0;
 }
 
@@ -516,7 +698,7 @@ void mmd_destroy(mmd_handle* h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
-                      &h->task_row, &h->task_k, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
+                      &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
                       &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count};
@@ -544,6 +726,29 @@ void mmd_reset_stats(mmd_handle* h) {
     h->launches = 0;
     h->n_clusters = 0;
     h->syrk_flops = 0.0;
+    h->solve_flops = 0.0;
+    h->n_batches = h->n_core_tasks = h->n_grouped = h->sum_sp = h->plan_us = h->adj_h2d_us = 0;
+}
+
+int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* solve_flops) {
+    if (!h) return 1;
+    if (counters) {
+        counters[0] = h->n_batches;
+        counters[1] = h->n_core_tasks;
+        counters[2] = h->n_grouped;
+        counters[3] = h->sum_sp;
+        counters[4] = h->plan_us;
+        counters[5] = h->adj_h2d_us;
+    }
+    if (solve_flops) *solve_flops = h->solve_flops;
+    return 0;
+}
+
+int mmd_set_group_size(mmd_handle* h, int group_size) {
+    if (!h) return 1;
+    if (group_size < 1 || group_size > 64) return fail(h, "mmd_set_group_size: group size must be 1..64");
+    h->group_size = group_size;
+    return 0;
 }
 
 int mmd_get_stats(mmd_handle* h, float stage_ms[MMD_N_STAGES], int64_t* n_launches, int64_t* n_clusters,

@@ -456,9 +456,43 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
 
     if (tid == 0) bad_pivot = 0;
 
+    // Prefix sharing: the first jc panels of L (and of W) belong to the group's core task.
+    const int s_p = task.s_p, jc = s_p / NB;
+    const double* core = task.core_work;                        // rows 0..s_p-1: L11, rows s_p..: W1; stride s_p
+    const long ldc = s_p;
+    if (jc > 0) {
+        // W1 -> the first s_p columns of this centre's W rows (the own panels extend them in place)
+        const int n2 = s_p / 2;
+        for (int e = tid; e < EVAL_PAD * n2; e += THREADS) {
+            const int r = e / n2, c2 = (e % n2) * 2;
+            *reinterpret_cast<double2*>(M + (long)(kp + r) * ld + c2) =
+                *reinterpret_cast<const double2*>(core + (long)(s_p + r) * ldc + c2);
+        }
+    }
+
     // ---------------- factorisation + forward solve, panel by panel ----------------
     for (int j = 0; j < nblk; ++j) {
         const int K = j * NB;
+        if (j < jc) {
+            // shared panel: L21[:, K..K+63] for this centre's own rows s_p..kp-1 only; the panel rows of L11 and the
+            // inverse of its diagonal block come from the core task
+            for (int e = tid; e < NB * NB; e += THREADS) {       // previous readers of Ism passed a barrier
+                const int r = e / NB, c = e % NB;
+                Ism[r * LDD + c] = core[(long)(K + r) * ldc + K + c];
+            }
+            const double* panel_rows = core + (long)K * ldc;
+            for (int u0 = 0; u0 < (kp - s_p) / 16; u0 += NWARPS) {
+                const int mrow = s_p + 16 * (u0 + warp);
+                Frag<8> acc;
+                auto a_row = [&](int r) -> const double* { return M + (long)(s_p + 16 * u0 + r) * ld; };
+                auto init = [&]() { strip_init<8>(acc, task, prm, false, mrow, K, lane); };
+                strip_gemm<false, 8>(acc, a_row, panel_rows, ldc, K / KC, pipe, init, tid, lane, warp);
+                strip_times_tri<false>(acc, Ism, stage, lane);
+                strip_store<8>(acc, M + (long)mrow * ld + K, ld, lane);
+            }
+            __syncthreads();
+            continue;
+        }
         const int n_a = kp / 16 - 4 * j;                        // strips of A from the diagonal block down
         const int n_strips = n_a + N_ESTRIPS;                   // = 4q + 1
         const double* panel_rows = M + (long)K * ld;            // L[K..K+63][0..K)
@@ -504,34 +538,62 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         __syncthreads();                                         // panel j complete (global writes visible CTA-wide)
     }
 
+    if (prm.core_only) {
+        if (tid == 0) prm.flags[task.centre] = bad_pivot;
+        return;
+    }
+
     // ---------------- backward solve: Zt_i = (W_i - sum_{p>i} Zt_p L_pi) L_ii^{-1} ----------------
+    // Rows of L below a shared panel (i < jc) come from two places: c0+64 .. s_p-1 from the core task, s_p .. kp-1 from
+    // this centre's own rows; the product is accumulated in two pipeline runs.
     for (int i = nblk - 1; i >= 0; --i) {
         const int c0 = i * NB, Kb = kp - (c0 + NB);
-        const double* lpanel = M + (long)(c0 + NB) * ld + c0;   // L[c0+64.., c0..c0+63], row-major (k x n)
+        const bool shared = i < jc;
+        const int Kb1 = shared ? s_p - (c0 + NB) : 0;            // k-extent served by the core task
+        const double* lpanel = M + (long)(c0 + NB + Kb1) * ld + c0;            // own rows, row-major (k x n)
+        const double* cpanel = core + (long)(c0 + NB) * ldc + c0;              // core rows (used when Kb1 > 0)
+        const double* dsrc = shared ? core + (long)c0 * ldc + c0 : M + (long)c0 * ld + c0;
+        const long dld = shared ? ldc : ld;
         for (int e = tid; e < NB * NB; e += THREADS) {           // previous readers of Ism passed a barrier
             const int r = e / NB, c = e % NB;
-            Ism[r * LDD + c] = M[(long)(c0 + r) * ld + c0 + c];
+            Ism[r * LDD + c] = dsrc[(long)r * dld + c];
         }
+        auto nop = [&]() {};
         for (int u0 = 0; u0 + NWARPS <= N_ESTRIPS; u0 += NWARPS) {
             double* zrows = M + (long)(kp + 16 * (u0 + warp)) * ld;
             Frag<8> acc;
-            auto a_row = [&](int r) -> const double* { return M + (long)(kp + 16 * u0 + r) * ld + c0 + NB; };
             auto init = [&]() { strip_load_neg<8>(acc, zrows + c0, ld, lane); };
-            strip_gemm<true, 8>(acc, a_row, lpanel, ld, Kb / KC, pipe, init, tid, lane, warp);
+            if (Kb1 > 0) {
+                auto a_row1 = [&](int r) -> const double* { return M + (long)(kp + 16 * u0 + r) * ld + c0 + NB; };
+                strip_gemm<true, 8>(acc, a_row1, cpanel, ldc, Kb1 / KC, pipe, init, tid, lane, warp);
+                auto a_row2 = [&](int r) -> const double* { return M + (long)(kp + 16 * u0 + r) * ld + c0 + NB + Kb1; };
+                strip_gemm<true, 8>(acc, a_row2, lpanel, ld, (Kb - Kb1) / KC, pipe, nop, tid, lane, warp);
+            } else {
+                auto a_row = [&](int r) -> const double* { return M + (long)(kp + 16 * u0 + r) * ld + c0 + NB; };
+                strip_gemm<true, 8>(acc, a_row, lpanel, ld, Kb / KC, pipe, init, tid, lane, warp);
+            }
             strip_times_tri<true>(acc, Ism, stage, lane);
             strip_store<8>(acc, zrows + c0, ld, lane);
         }
         {
             double* zrows = M + (long)(kp + 16 * (N_ESTRIPS - 1)) * ld;
             Frag<2> acc;
-            auto a_row = [&](int r) -> const double* { return r < 16 ? zrows + (long)r * ld + c0 + NB : nullptr; };
             auto init = [&]() { strip_load_neg<2>(acc, zrows + c0 + 16 * warp, ld, lane); };
-            strip_gemm<true, 2>(acc, a_row, lpanel, ld, Kb / KC, pipe, init, tid, lane, warp);
+            if (Kb1 > 0) {
+                auto a_row1 = [&](int r) -> const double* { return r < 16 ? zrows + (long)r * ld + c0 + NB : nullptr; };
+                strip_gemm<true, 2>(acc, a_row1, cpanel, ldc, Kb1 / KC, pipe, init, tid, lane, warp);
+                auto a_row2 = [&](int r) -> const double* { return r < 16 ? zrows + (long)r * ld + c0 + NB + Kb1 : nullptr; };
+                strip_gemm<true, 2>(acc, a_row2, lpanel, ld, (Kb - Kb1) / KC, pipe, nop, tid, lane, warp);
+            } else {
+                auto a_row = [&](int r) -> const double* { return r < 16 ? zrows + (long)r * ld + c0 + NB : nullptr; };
+                strip_gemm<true, 2>(acc, a_row, lpanel, ld, Kb / KC, pipe, init, tid, lane, warp);
+            }
             split_times_tri<true>(acc, Ism, pipe, lane, warp);
             strip_store<2>(acc, zrows + c0 + 16 * warp, ld, lane);
         }
         __syncthreads();                                         // Zt block visible before it is read as an operand
     }
+    if (tid == 0 && task.core_flag && *task.core_flag) bad_pivot = 1;
     if (tid == 0) prm.flags[task.centre] = bad_pivot;
 }
 

@@ -41,6 +41,13 @@ struct CentreTask {
     int centre;           // output slot (index into scores / flags)
     int k;                // this centre's neighbour count (ragged radius-mode neighbourhoods: searchlight.py:164-171)
     int kp;               // k rounded up to a multiple of 64: order of this centre's padded normal matrix
+    // Prefix sharing: the first s_p entries of loc / nbr (a multiple of 64, 0 = none) are common to a group of
+    // nearby centres; the leading s_p columns of L and of W = E L^{-T} were computed once for the group by a
+    // "core" task (k = kp = s_p) and are read from core_work (rows 0..s_p-1: L11 with inverted diagonal blocks,
+    // rows s_p..s_p+143: W1; row stride s_p).
+    int s_p;
+    const double* core_work;
+    const int* core_flag;     // non-positive pivot met while factoring the shared core
 };
 struct SolveParams {
     const CentreTask* tasks;
@@ -50,6 +57,7 @@ struct SolveParams {
     const __half* Xe;     // (V x EVAL_PAD) evaluation trials per vertex
     double* work;         // per task: (task.kp + EVAL_PAD) x task.kp doubles at the start of its stride
     int* flags;           // per task slot: 1 if a non-positive pivot was met
+    int core_only;        // 1: tasks are shared cores: factorisation + forward solve only (no backward solve)
 };
 size_t factor_solve_smem_bytes();
 cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s);
@@ -114,8 +122,12 @@ cudaError_t launch_pairwise_count(const double* dist, int r, int c, unsigned lon
 
 // ---- prep.cu -----------------------------------------------------------------------------
 // task t reads its neighbour list adjacency[task_row_off[t] .. + task_k[t]) and writes kp_max-strided rows
+// task_core_off / task_core_n (optional): the task's shared core, an ascending list inside `adjacency`
+// (task_core_n[t] entries at adjacency[task_core_off[t]..], a subset of the task's own list); the output is
+// ordered [core | remaining neighbours], both parts ascending.
 cudaError_t launch_prep_tasks(const int* adjacency, const long* task_row_off, const int* task_k, int k_max, int kp_max,
                               const long* task_union_off, const int* task_union_n, const int* union_vertices,
+                              const long* task_core_off, const int* task_core_n,
                               int n_vertices, int n_tasks, int* nbr_sorted, int* loc, int* bad_index_flag,
                               cudaStream_t s);
 __global__ void gather_rows_f16_kernel(const __half* Y, long ldy, const int* rows, int n_rows, int D, __half* out,

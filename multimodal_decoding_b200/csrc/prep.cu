@@ -13,7 +13,9 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
                                                          const int* __restrict__ task_k, int kp,
                                                          const long* __restrict__ task_union_off,
                                                          const int* __restrict__ task_union_n,
-                                                         const int* __restrict__ union_vertices, int n_vertices,
+                                                         const int* __restrict__ union_vertices,
+                                                         const long* __restrict__ task_core_off,
+                                                         const int* __restrict__ task_core_n, int n_vertices,
                                                          int* __restrict__ nbr_sorted, int* __restrict__ loc,
                                                          int* __restrict__ bad_index_flag) {
     extern __shared__ int sm[];                 // next power of two >= the largest k of the launch
@@ -46,10 +48,24 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
         }
     const int* uni = union_vertices + task_union_off[t];
     const int un = task_union_n[t];
-    for (int i = tid; i < kp; i += blockDim.x) {
+    const int n_core = task_core_n ? task_core_n[t] : 0;
+    const int* core = n_core ? adjacency + task_core_off[t] : nullptr;
+    for (int i = tid; i < kp; i += blockDim.x) nbr_sorted[(long)t * kp + i] = -1, loc[(long)t * kp + i] = -1;
+    __syncthreads();
+    for (int i = tid; i < k; i += blockDim.x) {
         int v = -1, pos = -1;
-        if (i < k) {
+        int dst = i;
+        {
             v = sm[i];
+            if (n_core) {                        // [core | rest]: both lists ascending, core is a subset of the row
+                int lo = 0, hi = n_core;
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (core[mid] < v) lo = mid + 1;
+                    else hi = mid;
+                }
+                dst = (lo < n_core && core[lo] == v) ? lo : n_core + (i - lo);
+            }
             int lo = 0, hi = un;                 // lower_bound
             while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
@@ -59,20 +75,21 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
             pos = lo;
             if (lo >= un || uni[lo] != v) atomicMax(bad_index_flag, 1);   // 1 = not in the union
         }
-        nbr_sorted[(long)t * kp + i] = v;
-        loc[(long)t * kp + i] = pos;
+        nbr_sorted[(long)t * kp + dst] = v;
+        loc[(long)t * kp + dst] = pos;
     }
 }
 
 cudaError_t launch_prep_tasks(const int* adjacency, const long* task_row_off, const int* task_k, int k_max, int kp_max,
                               const long* task_union_off, const int* task_union_n, const int* union_vertices,
+                              const long* task_core_off, const int* task_core_n,
                               int n_vertices, int n_tasks, int* nbr_sorted, int* loc, int* bad_index_flag,
                               cudaStream_t s) {
     int np2 = 1;
     while (np2 < k_max) np2 <<= 1;
     prep_tasks_kernel<<<n_tasks, 256, np2 * sizeof(int), s>>>(adjacency, task_row_off, task_k, kp_max, task_union_off,
-                                                             task_union_n, union_vertices, n_vertices, nbr_sorted,
-                                                             loc, bad_index_flag);
+                                                             task_union_n, union_vertices, task_core_off, task_core_n,
+                                                             n_vertices, nbr_sorted, loc, bad_index_flag);
     return cudaGetLastError();
 }
 

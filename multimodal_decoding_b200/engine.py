@@ -65,8 +65,10 @@ class Engine:
         if rc != 0:
             raise RuntimeError(self._lib.mmd_last_error(self._h).decode())
 
-    def configure(self, cluster_size=0, batch_centres=0, host_threads=0):
+    def configure(self, cluster_size=0, batch_centres=0, host_threads=0, group_size=0):
         self._check(self._lib.mmd_configure(self._h, cluster_size, batch_centres, host_threads))
+        if group_size:
+            self._check(self._lib.mmd_set_group_size(self._h, group_size))
 
     # -- adjacency ---------------------------------------------------------------------------
     def knn(self, coords, k: int, q_begin: int = 0, q_end: int | None = None):
@@ -236,5 +238,9 @@ class Engine:
         launches, clusters, flops = C.c_int64(), C.c_int64(), C.c_double()
         self._check(self._lib.mmd_get_stats(self._h, ms, C.byref(launches), C.byref(clusters), C.byref(flops)))
         names = [self._lib.mmd_stage_name(i).decode() for i in range(_lib.N_STAGES)]
+        cnt, solve = (C.c_int64 * 6)(), C.c_double()
+        self._check(self._lib.mmd_get_counters(self._h, cnt, C.byref(solve)))
         return {"stage_ms": dict(zip(names, [float(x) for x in ms])), "launches": launches.value,
-                "clusters": clusters.value, "syrk_flops": flops.value}
+                "clusters": clusters.value, "syrk_flops": flops.value, "batches": cnt[0], "core_tasks": cnt[1],
+                "grouped_centres": cnt[2], "sum_shared_prefix": cnt[3], "host_plan_ms": cnt[4] / 1e3,
+                "host_adjacency_h2d_ms": cnt[5] / 1e3, "solve_flops": solve.value}

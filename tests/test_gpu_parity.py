@@ -215,3 +215,36 @@ def test_dropin_custom_search_light_ragged(golden_dir):
     assert out.shape == (len(g["scores"]),) and out.dtype == object
     got = np.array([[d[k] for k in g["keys"]] for d in out])
     assert np.array_equal(got, g["scores"])
+
+
+def test_prefix_sharing_group_sizes(engine):
+    """Neighbouring centres factor their shared neighbours once (mmd_set_group_size).  The scores must not depend on
+    the group size and must equal the oracle's; the counters prove the shared path ran."""
+    from multimodal_decoding_b200 import synthetic as syn
+    mesh = syn.make_mesh(level=4, seed=5)                      # 2,562 vertices
+    trials = syn.make_trials(mesh, n_train=700, n_dims=64, seed=3)
+    inp = syn.make_searchlight_inputs(mesh, trials)
+    _, A = engine.knn(inp.coords, 300)
+    engine.upload(inp.X, inp.latents, inp.train_ids, inp.test_ids, inp.imagery_ids, orc.default_is_caption(140))
+    results = {}
+    try:
+        for g in (1, 2, 6, 16):
+            engine.configure(group_size=g)
+            engine.reset_stats()
+            results[g], flags = engine.searchlight(A, 1.0)
+            st = engine.stats()
+            assert flags.sum() == 0
+            if g == 1:
+                assert st["grouped_centres"] == 0 and st["core_tasks"] == 0
+            else:
+                assert st["grouped_centres"] > len(A) // 2 and st["core_tasks"] > 0
+                assert st["sum_shared_prefix"] >= 128 * st["grouped_centres"]
+    finally:
+        engine.configure(group_size=6)
+    sample = list(range(0, len(A), 61))
+    want = orc.search_light(inp.X, inp.latents, A, inp.train_ids, inp.test_ids, inp.imagery_ids, alpha=1.0,
+                            centres=sample)
+    for g, got in results.items():
+        assert np.abs(got[sample] - want).max() <= TOL, g
+        assert np.array_equal(got[sample], want), g
+        assert np.abs(got - results[1]).max() <= TOL, g
