@@ -84,6 +84,11 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
 int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
                     double* scores_out, int32_t* flags_out);
 
+/* mmd_searchlight for the int64 index matrix sklearn's kneighbors returns (searchlight.py:173), without a copy on
+ * the caller's side. */
+int mmd_searchlight_i64(mmd_handle* h, const int64_t* adjacency, int n_centres, int k, double alpha,
+                        double* scores_out, int32_t* flags_out);
+
 /* The same loop for ragged neighbourhoods, i.e. the radius branch of get_adjacency_matrix
  * (searchlight.py:164-171: one index array of its own length per centre).
  *   indices      concatenated vertex ids of all neighbourhoods, int32, HOST pointer
@@ -138,7 +143,7 @@ const char* mmd_stage_name(int i);
 int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* solve_flops);
 
 /* Prefix sharing: up to `group_size` neighbouring centres factor the part of their normal matrices that belongs to
- * the neighbours they all share only once (1 = off; default 6).  The scores do not depend on it. */
+ * the neighbours they all share only once (1 = off; default 8).  The scores do not depend on it. */
 int mmd_set_group_size(mmd_handle* h, int group_size);
 
 /* Tuning knobs (0 keeps the default): centres per cluster, max centres per batch. */

@@ -13,7 +13,7 @@ EVAL_PAD = 144
 
 EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload",
-    "mmd_searchlight", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
+    "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
 ]
 
@@ -52,6 +52,8 @@ def load():
     lib.mmd_upload.restype = i32
     lib.mmd_searchlight.argtypes = [vp, vp, i32, i32, dbl, vp, vp]
     lib.mmd_searchlight.restype = i32
+    lib.mmd_searchlight_i64.argtypes = [vp, vp, i32, i32, dbl, vp, vp]
+    lib.mmd_searchlight_i64.restype = i32
     lib.mmd_searchlight_ragged.argtypes = [vp, vp, vp, vp, i32, dbl, vp, vp]
     lib.mmd_searchlight_ragged.restype = i32
     lib.mmd_searchlight_null.argtypes = [vp, vp, i32, i32, dbl, vp, vp, i32, vp, vp, vp]

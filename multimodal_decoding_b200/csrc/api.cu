@@ -57,6 +57,25 @@ struct DevBuf {
     T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+struct PinnedBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t need) {
+        if (need <= bytes) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaHostAlloc(&p, need, cudaHostAllocDefault);
+        if (e == cudaSuccess) bytes = need;
+        return e;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
+    }
+};
+
 struct TimedSpan {
     cudaEvent_t a, b;
     int stage;
@@ -76,11 +95,12 @@ struct mmd_handle {
     DevBuf adj, union_vertices, task_row, task_k, task_core_off, task_core_n, core_work, group_flags, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
+    PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
     DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
     int n_perm = 0;
     std::vector<int> int_of_test;   // position in test_ids order -> internal evaluation row (captions first)
     // knobs
-    int cluster_size = 256, batch_centres = 2048, host_threads = 0, group_size = 6;
+    int cluster_size = 256, batch_centres = 2048, host_threads = 0, group_size = 8;
     // stats
     float stage_ms[MMD_N_STAGES] = {0};
     int64_t launches = 0, n_clusters = 0, n_batches = 0, n_core_tasks = 0, n_grouped = 0, sum_sp = 0, plan_us = 0,
@@ -555,36 +575,65 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     return 0;
 }
 
-int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_null = false, bool raw_yhat = false) {
+int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_null = false, bool raw_yhat = false,
+                    const int64_t* data64 = nullptr) {
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight");
-    const int n_centres = rows.n;
+    const int n_centres = rows_in.n;
+    int n_threads = h->host_threads > 0 ? h->host_threads : (int)std::thread::hardware_concurrency();
+    n_threads = std::max(1, std::min(n_threads, 32));
     int k_max = 0;
     for (int i = 0; i < n_centres; ++i) {
-        const int k = rows.len(i);
+        const int k = rows_in.len(i);
         if (k < 1 || k > h->V) return fail(h, "k=%d out of range (1..%d) for centre %d", k, h->V, i);
         if (k > h->n_train)
             return fail(h, "k=%d exceeds n_train=%d: the primal normal equations are rank deficient only through "
                            "alpha; the dual form is not implemented on this path", k, h->n_train);
         if (k > 2000) return fail(h, "k=%d exceeds the supported maximum of 2000", k);
         k_max = std::max(k_max, k);
-        if (!rows.off) break;              // rectangular: one length
+        if (!rows_in.off) break;              // rectangular: one length
     }
+    // Stage the adjacency in pinned memory as int32 (sklearn hands out int64 indices): the H2D copy then runs
+    // asynchronously while the host groups the centres.
+    const auto t_stage0 = std::chrono::steady_clock::now();
+    const size_t total = (size_t)rows_in.total();
+    CU(h->adj_host.ensure(std::max<size_t>(total, 1) * sizeof(int32_t)));
+    {
+        int32_t* dst = reinterpret_cast<int32_t*>(h->adj_host.p);
+        const int32_t* src32 = rows_in.data;
+        const int nt = (int)std::max<size_t>(1, std::min<size_t>(n_threads, total / (1 << 20) + 1));
+        auto conv = [&](int t) {
+            const size_t lo = total * t / nt, hi = total * (t + 1) / nt;
+            if (data64) {
+                for (size_t i = lo; i < hi; ++i) {
+                    const int64_t v = data64[i];
+                    dst[i] = (v < 0 || v > 0x7fffffff) ? -1 : (int32_t)v;     // out of range: reported by the device check
+                }
+            } else {
+                memcpy(dst + lo, src32 + lo, (hi - lo) * sizeof(int32_t));
+            }
+        };
+        std::vector<std::thread> pool;
+        for (int t = 1; t < nt; ++t) pool.emplace_back(conv, t);
+        conv(0);
+        for (auto& t : pool) t.join();
+    }
+    Rows rows = rows_in;
+    rows.data = reinterpret_cast<const int32_t*>(h->adj_host.p);
+    // adjacency rows, then (after grouping) the shared cores: at most half as many entries again
+    CU(h->adj.ensure((total + total / 2 + 2) * sizeof(int)));
+    CU(cudaMemcpyAsync(h->adj.p, rows.data, total * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    h->adj_h2d_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_stage0).count();
     const int kp = round_up(k_max, NB);
-    int n_threads = h->host_threads > 0 ? h->host_threads : (int)std::thread::hardware_concurrency();
-    n_threads = std::max(1, std::min(n_threads, 32));
 
     Plan plan;
     const auto t_plan0 = std::chrono::steady_clock::now();
     build_plan(rows, h->V, h->cluster_size, h->group_size, n_threads, plan);
     const auto t_plan1 = std::chrono::steady_clock::now();
     h->plan_us += std::chrono::duration_cast<std::chrono::microseconds>(t_plan1 - t_plan0).count();
-    // adjacency rows, then the groups' shared cores (read by the prep kernel like rows)
-    CU(h->adj.ensure(((size_t)rows.total() + plan.core_vert.size() + 1) * sizeof(int)));
-    CU(cudaMemcpyAsync(h->adj.p, rows.data, (size_t)rows.total() * sizeof(int), cudaMemcpyDefault, h->stream));
+    if (plan.core_vert.size() > total / 2) return fail(h, "internal: shared cores exceed their bound");
     if (!plan.core_vert.empty())
         CU(cudaMemcpyAsync(h->adj.as<int>() + rows.total(), plan.core_vert.data(), plan.core_vert.size() * sizeof(int),
                            cudaMemcpyDefault, h->stream));
-    h->adj_h2d_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_plan1).count();
     int sp_max = 0;
     for (size_t g = 0; g < plan.grp_sp.size(); ++g) {
         sp_max = std::max(sp_max, plan.grp_sp[g]);
@@ -645,9 +694,9 @@ int run_searchlight(mmd_handle* h, const Rows& rows, double alpha, bool with_nul
 }
 
 int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double* scores_out, int32_t* flags_out,
-                          const char* who) {
+                          const char* who, const int64_t* data64 = nullptr) {
     const int n_centres = rows.n;
-    if (run_searchlight(h, rows, alpha)) {
+    if (run_searchlight(h, rows, alpha, false, false, data64)) {
         cudaStreamSynchronize(h->stream);
         h->spans.clear();
         h->events_used = 0;
@@ -703,6 +752,7 @@ void mmd_destroy(mmd_handle* h) {
                       &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count};
     for (DevBuf* b : bufs) b->release();
+    h->adj_host.release();
     for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream);
     delete h;
@@ -966,6 +1016,18 @@ int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int 
     CU(cudaSetDevice(h->device));
     const Rows rows{adjacency, nullptr, k, nullptr, n_centres};
     return searchlight_and_fetch(h, rows, alpha, scores_out, flags_out, "mmd_searchlight");
+}
+
+int mmd_searchlight_i64(mmd_handle* h, const int64_t* adjacency, int n_centres, int k, double alpha, double* scores_out,
+                        int32_t* flags_out) {
+    if (!h) return 1;
+    if (!adjacency || !scores_out) return fail(h, "mmd_searchlight_i64: null pointer");
+    if (n_centres < 0) return fail(h, "mmd_searchlight_i64: negative centre count");
+    if (n_centres == 0) return 0;
+    if (is_device_ptr(adjacency)) return fail(h, "mmd_searchlight_i64: adjacency must be a host pointer");
+    CU(cudaSetDevice(h->device));
+    const Rows rows{nullptr, nullptr, k, nullptr, n_centres};
+    return searchlight_and_fetch(h, rows, alpha, scores_out, flags_out, "mmd_searchlight_i64", adjacency);
 }
 
 int mmd_searchlight_ragged(mmd_handle* h, const int32_t* indices, const int64_t* offsets, const int32_t* anchors,

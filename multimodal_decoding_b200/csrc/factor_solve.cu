@@ -437,6 +437,17 @@ __device__ __forceinline__ void factor_invert_block(double* D, double* I, int* b
     __syncthreads();
 }
 
+// 64x64 block (row stride ld, 16-byte aligned rows) -> shared memory with stride LDD, as one cp.async group.  The
+// next strip_gemm drains it (its final wait_group 0 + barrier), so the copy overlaps that product; the block is
+// only read afterwards (strip_times_tri / split_times_tri).
+__device__ __forceinline__ void load_block_async(double* dst, const double* __restrict__ src, long ld, int tid) {
+    for (int e = tid; e < NB * NB / 2; e += THREADS) {
+        const int r = e / (NB / 2), c = (e % (NB / 2)) * 2;
+        cp_async16(dst + r * LDD + c, src + (long)r * ld + c);
+    }
+    cp_async_commit();
+}
+
 __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams prm) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* pipe = reinterpret_cast<double*>(smem_raw);         // cp.async ring | diagonal block | strip staging
@@ -476,10 +487,7 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         if (j < jc) {
             // shared panel: L21[:, K..K+63] for this centre's own rows s_p..kp-1 only; the panel rows of L11 and the
             // inverse of its diagonal block come from the core task
-            for (int e = tid; e < NB * NB; e += THREADS) {       // previous readers of Ism passed a barrier
-                const int r = e / NB, c = e % NB;
-                Ism[r * LDD + c] = core[(long)(K + r) * ldc + K + c];
-            }
+            load_block_async(Ism, core + (long)K * ldc + K, ldc, tid);   // previous readers of Ism passed a barrier
             const double* panel_rows = core + (long)K * ldc;
             for (int u0 = 0; u0 < (kp - s_p) / 16; u0 += NWARPS) {
                 const int mrow = s_p + 16 * (u0 + warp);
@@ -554,10 +562,7 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         const double* cpanel = core + (long)(c0 + NB) * ldc + c0;              // core rows (used when Kb1 > 0)
         const double* dsrc = shared ? core + (long)c0 * ldc + c0 : M + (long)c0 * ld + c0;
         const long dld = shared ? ldc : ld;
-        for (int e = tid; e < NB * NB; e += THREADS) {           // previous readers of Ism passed a barrier
-            const int r = e / NB, c = e % NB;
-            Ism[r * LDD + c] = dsrc[(long)r * dld + c];
-        }
+        load_block_async(Ism, dsrc, dld, tid);                   // previous readers of Ism passed a barrier
         auto nop = [&]() {};
         for (int u0 = 0; u0 + NWARPS <= N_ESTRIPS; u0 += NWARPS) {
             double* zrows = M + (long)(kp + 16 * (u0 + warp)) * ld;

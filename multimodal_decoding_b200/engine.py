@@ -155,14 +155,17 @@ class Engine:
     def searchlight(self, adjacency, alpha: float = 1.0):
         if self._is_ragged(adjacency):
             return self.searchlight_ragged(adjacency, alpha)
-        adj = np.ascontiguousarray(np.asarray(adjacency, dtype=np.int32))
+        adj = np.asarray(adjacency)
         if adj.ndim != 2:
             raise ValueError("adjacency must be a sequence of index arrays")
+        # sklearn's int64 indices go to the library as they are (converted there by host threads)
+        wide = adj.dtype == np.int64
+        adj = np.ascontiguousarray(adj if wide else adj.astype(np.int32, copy=False))
         n, k = adj.shape
         scores = np.empty((n, _lib.N_SCORES), dtype=np.float64)
         flags = np.zeros(n, dtype=np.int32)
-        self._check(self._lib.mmd_searchlight(self._h, adj.ctypes.data, n, k, float(alpha), scores.ctypes.data,
-                                              flags.ctypes.data))
+        fn = self._lib.mmd_searchlight_i64 if wide else self._lib.mmd_searchlight
+        self._check(fn(self._h, adj.ctypes.data, n, k, float(alpha), scores.ctypes.data, flags.ctypes.data))
         return scores, flags
 
     def searchlight_null(self, adjacency, alpha, perm_test, perm_imagery):

@@ -240,7 +240,7 @@ def test_prefix_sharing_group_sizes(engine):
                 assert st["grouped_centres"] > len(A) // 2 and st["core_tasks"] > 0
                 assert st["sum_shared_prefix"] >= 128 * st["grouped_centres"]
     finally:
-        engine.configure(group_size=6)
+        engine.configure(group_size=8)
     sample = list(range(0, len(A), 61))
     want = orc.search_light(inp.X, inp.latents, A, inp.train_ids, inp.test_ids, inp.imagery_ids, alpha=1.0,
                             centres=sample)
