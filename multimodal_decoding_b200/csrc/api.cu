@@ -11,6 +11,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <future>
 #include <string>
 #include <thread>
 #include <vector>
@@ -207,39 +208,58 @@ struct Rows {
 
 constexpr int MIN_SHARED_PREFIX = 128;
 
-void build_plan(const Rows& rows, int V, int cluster_size, int group_size, int n_threads, Plan& plan) {
+// Spatial clusters of the centres of one call (cheap, sequential): cluster c owns members[cl_off[c] .. cl_off[c+1]).
+struct Clustering {
+    std::vector<int> centre_of;   // vertex -> the centre sitting on it (-1: none)
+    std::vector<int> cl_off, members;
+};
+
+void cluster_centres(const Rows& rows, int V, int cluster_size, Clustering& cl) {
     // greedy region growing: a seed takes its nearest still-unassigned centres (k-NN adjacency rows are ordered
     // by distance in the reference, the centre itself first; radius rows are in vertex order and scanned whole)
     const int n_centres = rows.n;
-    std::vector<int> centre_of(V, -1);
+    cl.centre_of.assign(V, -1);
     for (int i = n_centres - 1; i >= 0; --i) {
         const int v = rows.anchor(i);
-        if (v >= 0 && v < V) centre_of[v] = i;
+        if (v >= 0 && v < V) cl.centre_of[v] = i;
     }
     std::vector<char> assigned(n_centres, 0);
-    plan.cl_off.assign(1, 0);
-    plan.members.clear();
-    plan.members.reserve(n_centres);
+    cl.cl_off.assign(1, 0);
+    cl.members.clear();
+    cl.members.reserve(n_centres);
     for (int s = 0; s < n_centres; ++s) {
         if (assigned[s]) continue;
         assigned[s] = 1;
-        plan.members.push_back(s);
+        cl.members.push_back(s);
         int count = 1;
         const int32_t* row = rows.row(s);
         const int reach = rows.off ? rows.len(s) : std::min(rows.k, 3 * cluster_size);
         for (int j = 0; j < reach && count < cluster_size; ++j) {
             const int v = row[j];
             if (v < 0 || v >= V) continue;
-            const int c = centre_of[v];
+            const int c = cl.centre_of[v];
             if (c >= 0 && !assigned[c]) {
                 assigned[c] = 1;
-                plan.members.push_back(c);
+                cl.members.push_back(c);
                 ++count;
             }
         }
-        plan.cl_off.push_back((int)plan.members.size());
+        cl.cl_off.push_back((int)cl.members.size());
     }
-    const int n_clusters = (int)plan.cl_off.size() - 1;
+}
+
+// The plan of clusters [c_begin, c_end) of a clustering, with cluster indices local to that range: sorted unions and
+// prefix-sharing groups.  This is the expensive host step (every neighbour list is walked twice); run_searchlight
+// builds the plan of the next range while the GPU works on the current one.
+void build_plan(const Rows& rows, int V, const Clustering& cl, int c_begin, int c_end, int group_size, int n_threads,
+                Plan& plan) {
+    const int n_centres = rows.n;
+    const std::vector<int>& centre_of = cl.centre_of;
+    const int m0 = cl.cl_off[c_begin];
+    plan.cl_off.resize(c_end - c_begin + 1);
+    for (int c = c_begin; c <= c_end; ++c) plan.cl_off[c - c_begin] = cl.cl_off[c] - m0;
+    plan.members.assign(cl.members.begin() + m0, cl.members.begin() + cl.cl_off[c_end]);
+    const int n_clusters = c_end - c_begin;
     // unions and prefix-sharing groups, in parallel over clusters
     struct ClusterGroups {
         std::vector<int> order;       // the cluster's members, groups contiguous
@@ -575,6 +595,64 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     return 0;
 }
 
+// One chunk of clusters: upload its unions and shared cores, size the workspaces, run its batches.
+int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, int k_max, int kp, double alpha,
+              bool with_null, bool raw_yhat) {
+    const int n_clusters = (int)plan.cl_off.size() - 1;
+    if (to_device(h, h->union_vertices, plan.un_vert.data(), plan.un_vert.size())) return 1;
+    if (plan.core_vert.size() > total / 2) return fail(h, "internal: shared cores exceed their bound");
+    if (!plan.core_vert.empty())
+        CU(cudaMemcpyAsync(h->adj.as<int>() + total, plan.core_vert.data(), plan.core_vert.size() * sizeof(int),
+                           cudaMemcpyDefault, h->stream));
+    int sp_max = 0;
+    for (size_t g = 0; g < plan.grp_sp.size(); ++g) {
+        sp_max = std::max(sp_max, plan.grp_sp[g]);
+        if (plan.grp_sp[g] > 0) {
+            h->n_grouped += plan.grp_off[g + 1] - plan.grp_off[g];
+            h->sum_sp += (int64_t)plan.grp_sp[g] * (plan.grp_off[g + 1] - plan.grp_off[g]);
+        }
+    }
+
+    // batches: whole clusters, at most batch_centres centres
+    std::vector<int> batch_start(1, 0);
+    size_t max_pool = 0, cur_pool = 0;
+    int cur_tasks = 0, max_tasks = 0, cur_core = 0, max_core = 0;
+    for (int c = 0; c < n_clusters; ++c) {
+        const int m = plan.cl_off[c + 1] - plan.cl_off[c];
+        int n_core_c = 0;
+        for (int g = plan.cl_grp_off[c]; g < plan.cl_grp_off[c + 1]; ++g) n_core_c += plan.grp_sp[g] > 0;
+        const size_t u = (size_t)(plan.un_off[c + 1] - plan.un_off[c]);
+        const size_t g = u * round_up((int)u, 8);
+        if (cur_tasks > 0 && cur_tasks + m > h->batch_centres) {
+            batch_start.push_back(c);
+            cur_tasks = 0;
+            cur_pool = 0;
+            cur_core = 0;
+        }
+        cur_tasks += m;
+        cur_pool += g;
+        cur_core += n_core_c;
+        max_core = std::max(max_core, cur_core);
+        max_tasks = std::max(max_tasks, cur_tasks);
+        max_pool = std::max(max_pool, cur_pool);
+    }
+    batch_start.push_back(n_clusters);
+
+    // workspaces only grow; a growing buffer is freed first, which waits for the kernels still using it
+    CU(h->gram_pool.ensure(max_pool * sizeof(double)));
+    CU(h->work.ensure((size_t)max_tasks * (kp + EVAL_PAD) * kp * sizeof(double)));
+    CU(h->yhat.ensure((size_t)max_tasks * YHAT_ROWS * h->Dp * sizeof(double)));
+    CU(h->nbr_sorted.ensure((size_t)(max_tasks + max_core) * kp * sizeof(int)));
+    CU(h->loc.ensure((size_t)(max_tasks + max_core) * kp * sizeof(int)));
+    CU(h->core_work.ensure(std::max<size_t>((size_t)max_core * (sp_max + EVAL_PAD) * sp_max, 1) * sizeof(double)));
+    CU(h->group_flags.ensure(std::max<size_t>(max_core, 1) * sizeof(int)));
+    if (with_null) CU(h->dist.ensure((size_t)max_tasks * NULL_DIST_ROWS * EVAL_PAD * sizeof(double)));
+
+    for (size_t b = 0; b + 1 < batch_start.size(); ++b)
+        if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, sp_max, alpha, with_null, raw_yhat)) return 1;
+    return 0;
+}
+
 int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_null = false, bool raw_yhat = false,
                     const int64_t* data64 = nullptr) {
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight");
@@ -625,72 +703,46 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     h->adj_h2d_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_stage0).count();
     const int kp = round_up(k_max, NB);
 
-    Plan plan;
-    const auto t_plan0 = std::chrono::steady_clock::now();
-    build_plan(rows, h->V, h->cluster_size, h->group_size, n_threads, plan);
-    const auto t_plan1 = std::chrono::steady_clock::now();
-    h->plan_us += std::chrono::duration_cast<std::chrono::microseconds>(t_plan1 - t_plan0).count();
-    if (plan.core_vert.size() > total / 2) return fail(h, "internal: shared cores exceed their bound");
-    if (!plan.core_vert.empty())
-        CU(cudaMemcpyAsync(h->adj.as<int>() + rows.total(), plan.core_vert.data(), plan.core_vert.size() * sizeof(int),
-                           cudaMemcpyDefault, h->stream));
-    int sp_max = 0;
-    for (size_t g = 0; g < plan.grp_sp.size(); ++g) {
-        sp_max = std::max(sp_max, plan.grp_sp[g]);
-        if (plan.grp_sp[g] > 0) {
-            h->n_grouped += plan.grp_off[g + 1] - plan.grp_off[g];
-            h->sum_sp += (int64_t)plan.grp_sp[g] * (plan.grp_off[g + 1] - plan.grp_off[g]);
-        }
-    }
-    const int n_clusters = (int)plan.cl_off.size() - 1;
-    h->n_clusters += n_clusters;
-    if (to_device(h, h->union_vertices, plan.un_vert.data(), plan.un_vert.size())) return 1;
-
-    // batches: whole clusters, at most batch_centres centres
-    std::vector<int> batch_start(1, 0);
-    size_t max_pool = 0, cur_pool = 0;
-    int cur_tasks = 0, max_tasks = 0, cur_core = 0, max_core = 0;
-    for (int c = 0; c < n_clusters; ++c) {
-        const int m = plan.cl_off[c + 1] - plan.cl_off[c];
-        int n_core_c = 0;
-        for (int g = plan.cl_grp_off[c]; g < plan.cl_grp_off[c + 1]; ++g) n_core_c += plan.grp_sp[g] > 0;
-        const size_t u = (size_t)(plan.un_off[c + 1] - plan.un_off[c]);
-        const size_t g = u * round_up((int)u, 8);
-        if (cur_tasks > 0 && cur_tasks + m > h->batch_centres) {
-            batch_start.push_back(c);
-            cur_tasks = 0;
-            cur_pool = 0;
-            cur_core = 0;
-        }
-        cur_tasks += m;
-        cur_pool += g;
-        cur_core += n_core_c;
-        max_core = std::max(max_core, cur_core);
-        max_tasks = std::max(max_tasks, cur_tasks);
-        max_pool = std::max(max_pool, cur_pool);
-    }
-    batch_start.push_back(n_clusters);
-
-    CU(h->gram_pool.ensure(max_pool * sizeof(double)));
-    CU(h->work.ensure((size_t)max_tasks * (kp + EVAL_PAD) * kp * sizeof(double)));
-    CU(h->yhat.ensure((size_t)max_tasks * YHAT_ROWS * h->Dp * sizeof(double)));
-    CU(h->nbr_sorted.ensure((size_t)(max_tasks + max_core) * kp * sizeof(int)));
-    CU(h->loc.ensure((size_t)(max_tasks + max_core) * kp * sizeof(int)));
-    CU(h->core_work.ensure(std::max<size_t>((size_t)max_core * (sp_max + EVAL_PAD) * sp_max, 1) * sizeof(double)));
-    CU(h->group_flags.ensure(std::max<size_t>(max_core, 1) * sizeof(int)));
     CU(h->scores.ensure((size_t)n_centres * MMD_N_SCORES * sizeof(double)));
     CU(h->flags.ensure((size_t)n_centres * sizeof(int)));
     CU(h->misc_flag.ensure(sizeof(int)));
     CU(cudaMemsetAsync(h->misc_flag.p, 0, sizeof(int), h->stream));
     CU(cudaMemsetAsync(h->flags.p, 0, (size_t)n_centres * sizeof(int), h->stream));
-    if (with_null) {
-        CU(h->dist.ensure((size_t)max_tasks * NULL_DIST_ROWS * EVAL_PAD * sizeof(double)));
-        CU(h->null_out.ensure((size_t)n_centres * h->n_perm * 6 * sizeof(double)));
-    }
+    if (with_null) CU(h->null_out.ensure((size_t)n_centres * h->n_perm * 6 * sizeof(double)));
 
-    for (size_t b = 0; b + 1 < batch_start.size(); ++b)
-        if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, sp_max, alpha, with_null, raw_yhat)) return 1;
-    return 0;
+    // Clusters for the whole call, then plans for ranges of clusters ("chunks" of ~6 batches): the plan of chunk
+    // i+1 is built by host threads while the GPU executes chunk i.
+    auto t_host0 = std::chrono::steady_clock::now();
+    Clustering cl;
+    cluster_centres(rows, h->V, h->cluster_size, cl);
+    const int n_clusters = (int)cl.cl_off.size() - 1;
+    h->n_clusters += n_clusters;
+    std::vector<int> chunk_start(1, 0);
+    for (int c = 0, acc = 0; c < n_clusters; ++c) {
+        acc += cl.cl_off[c + 1] - cl.cl_off[c];
+        if (acc >= 6 * h->batch_centres && c + 1 < n_clusters) {
+            chunk_start.push_back(c + 1);
+            acc = 0;
+        }
+    }
+    chunk_start.push_back(n_clusters);
+    const int n_chunks = (int)chunk_start.size() - 1;
+    Plan plans[2];
+    const int group_size = h->group_size, V = h->V;
+    auto plan_chunk = [&, group_size, V, n_threads](int i) {
+        build_plan(rows, V, cl, chunk_start[i], chunk_start[i + 1], group_size, n_threads, plans[i & 1]);
+    };
+    std::future<void> pending = std::async(std::launch::async, plan_chunk, 0);
+    int rc = 0;
+    for (int i = 0; i < n_chunks && rc == 0; ++i) {
+        pending.get();                                     // exposed host time: only what the GPU did not hide
+        h->plan_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_host0).count();
+        if (i + 1 < n_chunks) pending = std::async(std::launch::async, plan_chunk, i + 1);
+        rc = run_chunk(h, rows, plans[i & 1], total, k_max, kp, alpha, with_null, raw_yhat);
+        t_host0 = std::chrono::steady_clock::now();
+    }
+    if (pending.valid()) pending.wait();                   // an error path must not leave the planner running
+    return rc;
 }
 
 int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double* scores_out, int32_t* flags_out,
