@@ -123,6 +123,25 @@ int mmd_dist_mat_to_pairwise_acc(mmd_handle* h, const double* dist_mat, int n_ro
 int mmd_pairwise_accuracy(mmd_handle* h, const double* latents, int n_lat, const double* predictions, int n_pred,
                           int n_dims, int standardize_predictions, int standardize_latents, double* acc_out);
 
+/* Group-level statistics on the score maps the searchlight writes (HOST buffers).
+ *   mmd_ttest_1samp     calc_image_t_values(data, popmean, sigma=sigma): per vertex the one-sample t-value of
+ *                       `data[:, v] - popmean` over subjects, NaN where all subjects agree
+ *                       (analyses/decoding/searchlight/searchlight_permutation_testing.py:213-258);
+ *                       data (n_subjects x n_vertices) float64, t_out (n_vertices) float64; flags bit 0: the variance
+ *                       floor is sigma * var ("relative", the reference's default) instead of sigma; bit 1: NaN where
+ *                       all subjects agree (calc_t_value) -- without it the plain ttest_1samp_no_p quotient
+ *   mmd_tfce            calc_tfce_values for one hemisphere and many maps (analyses/cluster_analysis.py:248-312, cluster
+ *                       extent = number of vertices): values (n_maps x n_vertices) float64, edges (n_edges x 2) int32
+ *                       vertex pairs of the mesh, dh <= 0 = "auto" (max / 100); tfce_out (n_maps x n_vertices) float32
+ *   mmd_cluster_labels  calc_clusters at one threshold (analyses/cluster_analysis.py:15-75): labels_out[v] = smallest
+ *                       vertex id of v's cluster, -1 for vertices outside clusters */
+int mmd_ttest_1samp(mmd_handle* h, const double* data, int n_subjects, int n_vertices, double popmean, double sigma,
+                    int flags, double* t_out);
+int mmd_tfce(mmd_handle* h, const double* values, int n_maps, int n_vertices, const int32_t* edges, int n_edges,
+             double h_exponent, double e_exponent, double dh, float* tfce_out);
+int mmd_cluster_labels(mmd_handle* h, const double* values, int n_vertices, const int32_t* edges, int n_edges,
+                       double threshold, int32_t* labels_out);
+
 /* Test/diagnostic hook: predictions of one centre, (143 x n_dims) float64 in the internal row order
  * [caption test trials, image test trials, imagery trials]; HOST pointer. */
 int mmd_predict_centre(mmd_handle* h, const int32_t* neighbours, int k, double alpha, double* yhat_out);

@@ -15,6 +15,7 @@ EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload",
     "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
+    "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels",
 ]
 
 _lib = None
@@ -64,6 +65,12 @@ def load():
     lib.mmd_dist_mat_to_pairwise_acc.restype = i32
     lib.mmd_pairwise_accuracy.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, C.POINTER(dbl)]
     lib.mmd_pairwise_accuracy.restype = i32
+    lib.mmd_ttest_1samp.argtypes = [vp, vp, i32, i32, dbl, dbl, i32, vp]
+    lib.mmd_ttest_1samp.restype = i32
+    lib.mmd_tfce.argtypes = [vp, vp, i32, i32, vp, i32, dbl, dbl, dbl, vp]
+    lib.mmd_tfce.restype = i32
+    lib.mmd_cluster_labels.argtypes = [vp, vp, i32, vp, i32, dbl, vp]
+    lib.mmd_cluster_labels.restype = i32
     lib.mmd_predict_centre.argtypes = [vp, vp, i32, dbl, vp]
     lib.mmd_predict_centre.restype = i32
     lib.mmd_get_stats.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(i64), C.POINTER(i64), C.POINTER(dbl)]

@@ -97,6 +97,7 @@ struct mmd_handle {
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
     PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
+    DevBuf st_in, st_edges, st_label, st_count, st_out;     // group-level statistics
     DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
     int n_perm = 0;
     std::vector<int> int_of_test;   // position in test_ids order -> internal evaluation row (captions first)
@@ -801,7 +802,7 @@ void mmd_destroy(mmd_handle* h) {
     DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
                       &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
-                      &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
+                      &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count};
     for (DevBuf* b : bufs) b->release();
     h->adj_host.release();
@@ -1228,6 +1229,76 @@ int mmd_dist_mat_to_pairwise_acc(mmd_handle* h, const double* dist_mat, int n_ro
     CU(cudaStreamSynchronize(h->stream));
     const long rows = n_rows < n_cols ? n_rows : n_cols;
     *acc_out = (double)count / (double)((long)n_rows * n_cols - rows);
+    return 0;
+}
+
+// ---- group-level statistics on score maps (HOST buffers) ----
+int mmd_ttest_1samp(mmd_handle* h, const double* data, int n_subjects, int n_vertices, double popmean, double sigma,
+                    int flags, double* t_out) {
+    if (!h) return 1;
+    if (!data || !t_out) return fail(h, "mmd_ttest_1samp: null pointer");
+    if (n_subjects < 2 || n_subjects > 128) return fail(h, "mmd_ttest_1samp: 2..128 subjects are supported (got %d)", n_subjects);
+    if (n_vertices < 1) return fail(h, "mmd_ttest_1samp: empty map");
+    CU(cudaSetDevice(h->device));
+    if (to_device(h, h->st_in, data, (size_t)n_subjects * n_vertices)) return 1;
+    CU(h->st_out.ensure((size_t)n_vertices * sizeof(double)));
+    CU(launch_ttest(h->st_in.as<double>(), n_subjects, n_vertices, popmean, sigma, flags & 1, (flags >> 1) & 1, h->st_out.as<double>(),
+                    h->stream));
+    h->launches += 1;
+    CU(cudaMemcpyAsync(t_out, h->st_out.p, (size_t)n_vertices * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+static int check_edges(mmd_handle* h, const int32_t* edges, int n_edges, int n_vertices, const char* who) {
+    if (n_edges < 0 || (n_edges > 0 && !edges)) return fail(h, "%s: bad edge list", who);
+    for (long i = 0; i < 2L * n_edges; ++i)
+        if (edges[i] < 0 || edges[i] >= n_vertices) return fail(h, "%s: edge endpoint %d outside [0, %d)", who, edges[i], n_vertices);
+    return 0;
+}
+
+int mmd_tfce(mmd_handle* h, const double* values, int n_maps, int n_vertices, const int32_t* edges, int n_edges,
+             double h_exponent, double e_exponent, double dh, float* tfce_out) {
+    if (!h) return 1;
+    if (!values || !tfce_out) return fail(h, "mmd_tfce: null pointer");
+    if (n_maps < 1 || n_vertices < 1) return fail(h, "mmd_tfce: empty input");
+    if (check_edges(h, edges, n_edges, n_vertices, "mmd_tfce")) return 1;
+    CU(cudaSetDevice(h->device));
+    if (to_device(h, h->st_edges, edges, (size_t)2 * std::max(n_edges, 1))) return 1;
+    const int chunk = std::max(1, std::min(n_maps, (int)std::min<size_t>(4096, ((size_t)2 << 30) / ((size_t)n_vertices * 8))));
+    CU(h->st_label.ensure((size_t)chunk * n_vertices * sizeof(int)));
+    CU(h->st_count.ensure((size_t)chunk * n_vertices * sizeof(int)));
+    CU(h->st_out.ensure((size_t)chunk * n_vertices * sizeof(float)));
+    for (int m0 = 0; m0 < n_maps; m0 += chunk) {
+        const int n = std::min(chunk, n_maps - m0);
+        if (to_device(h, h->st_in, values + (size_t)m0 * n_vertices, (size_t)n * n_vertices)) return 1;
+        CU(launch_tfce(h->st_in.as<double>(), n, n_vertices, h->st_edges.as<int>(), n_edges, h_exponent, e_exponent, dh,
+                       h->st_label.as<int>(), h->st_count.as<int>(), h->st_out.as<float>(), h->stream));
+        h->launches += 1;
+        CU(cudaMemcpyAsync(tfce_out + (size_t)m0 * n_vertices, h->st_out.p, (size_t)n * n_vertices * sizeof(float),
+                           cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+int mmd_cluster_labels(mmd_handle* h, const double* values, int n_vertices, const int32_t* edges, int n_edges,
+                       double threshold, int32_t* labels_out) {
+    if (!h) return 1;
+    if (!values || !labels_out) return fail(h, "mmd_cluster_labels: null pointer");
+    if (n_vertices < 1) return fail(h, "mmd_cluster_labels: empty map");
+    if (check_edges(h, edges, n_edges, n_vertices, "mmd_cluster_labels")) return 1;
+    CU(cudaSetDevice(h->device));
+    if (to_device(h, h->st_edges, edges, (size_t)2 * std::max(n_edges, 1))) return 1;
+    if (to_device(h, h->st_in, values, (size_t)n_vertices)) return 1;
+    CU(h->st_label.ensure((size_t)n_vertices * sizeof(int)));
+    CU(h->st_count.ensure((size_t)n_vertices * sizeof(int)));
+    CU(h->st_out.ensure((size_t)n_vertices * sizeof(int)));
+    CU(launch_cluster_labels(h->st_in.as<double>(), n_vertices, h->st_edges.as<int>(), n_edges, threshold,
+                             h->st_label.as<int>(), h->st_count.as<int>(), h->st_out.as<int>(), h->stream));
+    h->launches += 1;
+    CU(cudaMemcpyAsync(labels_out, h->st_out.p, (size_t)n_vertices * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
     return 0;
 }
 

@@ -138,6 +138,16 @@ __global__ void gather_rows_f16_kernel(const __half* Y, long ldy, const int* row
 cudaError_t launch_knn(const double* coords, int V, int k, int q_begin, int q_end, int64_t* idx_out,
                        double* dist_out, int* overflow_flag, cudaStream_t s);
 
+// ---- stats.cu ----------------------------------------------------------------------------
+// data: (n_subjects x V) float64; t_out: (V).  relative: the "hat" limit is sigma * var (per-vertex call), else sigma.
+cudaError_t launch_ttest(const double* data, int n_subjects, int V, double popmean, double sigma, int relative,
+                         int constant_is_nan, double* t_out, cudaStream_t s);
+// values: (n_maps x V) float64; edges: (E x 2) int32; label_ws / count_ws: (n_maps x V) int32 workspaces; out: (n_maps x V)
+cudaError_t launch_tfce(const double* values, int n_maps, int V, const int* edges, int E, double h, double e, double dh,
+                        int* label_ws, int* count_ws, float* out, cudaStream_t s);
+cudaError_t launch_cluster_labels(const double* values, int V, const int* edges, int E, double threshold, int* label_ws,
+                                  int* count_ws, int* labels_out, cudaStream_t s);
+
 // ---- radius.cu ---------------------------------------------------------------------------
 cudaError_t launch_radius_count(const double* coords, int V, double radius, int q_begin, int q_end, int* counts,
                                 cudaStream_t s);

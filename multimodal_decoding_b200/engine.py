@@ -221,6 +221,40 @@ class Engine:
                                                     int(bool(standardize_latents)), C.byref(acc)))
         return acc.value
 
+    # -- group-level statistics on score maps -----------------------------------
+    @staticmethod
+    def _edges(edges):
+        e = np.ascontiguousarray(np.asarray(edges, dtype=np.int32))
+        if e.ndim != 2 or e.shape[1] != 2:
+            raise ValueError("edges must be (n_edges, 2) vertex pairs")
+        return e
+
+    def ttest_1samp(self, data, popmean: float, sigma: float = 0.0, relative: bool = True, constant_is_nan: bool = True):
+        d = self._f64(data, "data")
+        out = np.empty(d.shape[1], dtype=np.float64)
+        self._check(self._lib.mmd_ttest_1samp(self._h, d.ctypes.data, d.shape[0], d.shape[1], float(popmean),
+                                              float(sigma), int(bool(relative)) | (int(bool(constant_is_nan)) << 1),
+                                              out.ctypes.data))
+        return out
+
+    def tfce(self, values, edges, h: float = 2.0, e: float = 1.0, dh: float = 0.1):
+        """values: (V,) or (n_maps, V); returns float32 of the same shape."""
+        v = np.asarray(values, dtype=np.float64)
+        maps = np.ascontiguousarray(np.atleast_2d(v))
+        ed = self._edges(edges)
+        out = np.empty(maps.shape, dtype=np.float32)
+        self._check(self._lib.mmd_tfce(self._h, maps.ctypes.data, maps.shape[0], maps.shape[1], ed.ctypes.data, len(ed),
+                                       float(h), float(e), float(dh), out.ctypes.data))
+        return out.reshape(v.shape)
+
+    def cluster_labels(self, values, edges, threshold: float):
+        v = np.ascontiguousarray(np.asarray(values, dtype=np.float64).ravel())
+        ed = self._edges(edges)
+        out = np.empty(len(v), dtype=np.int32)
+        self._check(self._lib.mmd_cluster_labels(self._h, v.ctypes.data, len(v), ed.ctypes.data, len(ed),
+                                                 float(threshold), out.ctypes.data))
+        return out
+
     def predict_centre(self, neighbours, alpha: float = 1.0):
         nb = np.ascontiguousarray(np.asarray(neighbours, dtype=np.int32))
         out = np.empty((self.n_eval, self.n_dims), dtype=np.float64)

@@ -4,7 +4,7 @@ Run from the repo root inside the build container (needs /root/reference):
 
     python tests/golden/make_golden.py
 
-Outputs (committed):  searchlight_small.npz, searchlight_smooth.npz, searchlight_radius.npz, knn_small.npz,
+Outputs (committed):  searchlight_small.npz, searchlight_smooth.npz, searchlight_radius.npz, group_stats.npz, knn_small.npz,
 eval_cases.npz, null_distr_small.npz, gridsearch_small.npz.
 Each file stores the exact inputs next to the reference outputs so the tests never depend on
 random-stream stability.
@@ -88,6 +88,58 @@ def radius_case():
                         n_imagery=len(inp.imagery_ids), alpha=1.0, scores=out, keys=np.array(KEYS))
     print("radius", out.shape, "neighbours min/mean/max", lens.min(), lens.mean().round(1), lens.max(),
           "mean", out.mean(0).round(3))
+
+
+def stats_case():
+    """Group-level statistics (SURVEY.md §8f #3): the unmodified t-map and TFCE functions on synthetic maps."""
+    import importlib
+    import types
+    sys.modules.setdefault("h5py", types.ModuleType("h5py"))          # only used for file I/O in that module
+    ref_perm = importlib.import_module("analyses.decoding.searchlight.searchlight_permutation_testing")
+    ref_clu = importlib.import_module("analyses.cluster_analysis")
+    rng = np.random.default_rng(17)
+    out = {}
+    meshes = {"left": syn.make_mesh(level=4, seed=31), "right": syn.make_mesh(level=4, seed=32)}
+    hemis = list(ref_clu.HEMIS)
+    t_values, edge_dicts = {}, {}
+    for hemi in hemis:
+        mesh = meshes[hemi]
+        edges = syn.mesh_edges(mesh.faces)
+        edges = np.array([(a, b) if a < b else (b, a) for a, b in edges])
+        lengths = np.sqrt(((mesh.coords[edges[:, 0]] - mesh.coords[edges[:, 1]]) ** 2).sum(1))
+        edge_dicts[hemi] = {(int(a), int(b)): float(l) for (a, b), l in zip(edges, lengths)}
+        v = len(mesh.coords)
+        # per-subject accuracy maps: chance 0.5 plus smooth blobs of signal; a few constant / NaN vertices
+        centres = mesh.coords[rng.integers(0, v, 6)]
+        d2 = ((mesh.coords[:, None, :] - centres[None]) ** 2).sum(-1)
+        signal = (0.08 * np.exp(-0.5 * d2 / 25.0 ** 2)).sum(1)
+        data = 0.5 + signal[None] + 0.03 * rng.standard_normal((6, v))
+        data[:, 5] = 0.5
+        data[:, 77] = data[0, 77]
+        data[2, 300:310] = np.nan
+        t = ref_perm.calc_image_t_values(data, 0.5)
+        t_sigma = ref_perm.calc_image_t_values(data, 0.5, sigma=1e-3)
+        t_values[hemi] = {"m": t}
+        out[f"{hemi}_edges"], out[f"{hemi}_data"], out[f"{hemi}_t"], out[f"{hemi}_t_sigma"] = edges, data, t, t_sigma
+        thr = 2.5
+        cl = ref_clu.calc_clusters(t, thr, edge_dicts[hemi], return_clusters=True)["clusters"]
+        lab = np.full(v, -1, dtype=np.int64)
+        for i, c in enumerate(sorted(cl, key=min)):
+            lab[list(c)] = i
+        out[f"{hemi}_cluster_threshold"], out[f"{hemi}_cluster_labels"] = thr, lab
+    for tag, kw in {"default": dict(), "h1_e05_dh02": dict(h=1, e=0.5, dh=0.2), "auto": dict(dh=0)}.items():
+        tf = ref_clu.calc_tfce_values(t_values, edge_dicts, "m", **kw)
+        for hemi in hemis:
+            out[f"{hemi}_tfce_{tag}"] = tf[hemi]["m"]
+    neg = {hemi: {"m": -np.abs(t_values[hemi]["m"])} for hemi in hemis}
+    out["left_tfce_nonpositive"] = ref_clu.calc_tfce_values(neg, edge_dicts, "m")["left"]["m"]
+    x = rng.standard_normal((6, 40)) + 0.3
+    out["ttest_x"], out["ttest_t"] = x, ref_perm.ttest_1samp_no_p(x)
+    out["ttest_t_rel"] = ref_perm.ttest_1samp_no_p(x, sigma=1e-2)
+    out["ttest_t_abs"] = ref_perm.ttest_1samp_no_p(x, sigma=1e-2, method="absolute")
+    np.savez_compressed(os.path.join(HERE, "group_stats.npz"), **out)
+    print("stats", {k: (np.asarray(v).shape, str(np.asarray(v).dtype)) for k, v in out.items() if "tfce" in k},
+          "max tfce", float(np.nanmax(out["left_tfce_default"])))
 
 
 def eval_cases():
@@ -186,6 +238,7 @@ if __name__ == "__main__":
                      seed=2, training_mode="captions")
     knn_case()
     radius_case()
+    stats_case()
     eval_cases()
     null_distr_case()
     gridsearch_case()

@@ -126,3 +126,29 @@ def test_gridsearch_semantics(golden_dir, tag):
     pred = x[n:].astype(np.float64) @ w
     assert np.allclose(pred, g[f"{tag}_pred_test"], rtol=2e-3, atol=2e-3)
     assert orc.kfold_bounds(103, 5) == [(0, 21), (21, 42), (42, 63), (63, 83), (83, 103)]
+
+
+# ---- group-level statistics --------------------------------------------------------------
+def test_group_stats_oracle_matches_reference(golden_dir):
+    from oracle import stats_oracle as so
+    g = _load(golden_dir, "group_stats.npz")
+    assert np.array_equal(so.ttest_1samp_no_p(g["ttest_x"]), g["ttest_t"])
+    assert np.array_equal(so.ttest_1samp_no_p(g["ttest_x"], sigma=1e-2), g["ttest_t_rel"])
+    assert np.array_equal(so.ttest_1samp_no_p(g["ttest_x"], sigma=1e-2, method="absolute"), g["ttest_t_abs"])
+    for hemi in ("left", "right"):
+        t = so.calc_image_t_values(g[f"{hemi}_data"], 0.5)
+        assert np.array_equal(t, g[f"{hemi}_t"], equal_nan=True)
+        assert np.isnan(t[5]) and np.isnan(t[77]) and np.isnan(t[300:310]).all()
+        assert np.array_equal(so.calc_image_t_values(g[f"{hemi}_data"], 0.5, sigma=1e-3), g[f"{hemi}_t_sigma"],
+                              equal_nan=True)
+        edges = g[f"{hemi}_edges"]
+        labels, sizes = so.clusters_at(t, edges, float(g[f"{hemi}_cluster_threshold"]))
+        want = g[f"{hemi}_cluster_labels"]
+        assert np.array_equal(labels >= 0, want >= 0)
+        # same partition (label names differ): vertices share a label here iff they share one there
+        pairs = set(zip(labels[labels >= 0].tolist(), want[want >= 0].tolist()))
+        assert len(pairs) == len(sizes) == want.max() + 1
+        assert np.array_equal(so.tfce(t, edges), g[f"{hemi}_tfce_default"])
+        assert np.array_equal(so.tfce(t, edges, h=1, e=0.5, dh=0.2), g[f"{hemi}_tfce_h1_e05_dh02"])
+        assert np.array_equal(so.tfce(t, edges, dh=0), g[f"{hemi}_tfce_auto"])
+    assert not so.tfce(-np.abs(g["left_t"]), g["left_edges"]).any() and not g["left_tfce_nonpositive"].any()
