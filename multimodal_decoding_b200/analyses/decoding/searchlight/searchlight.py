@@ -42,6 +42,14 @@ def get_engine(device: int | None = None) -> Engine:
         device = int(os.environ.get("LOCAL_RANK", "0"))
     if device not in _ENGINES:
         _ENGINES[device] = Engine(device)
+        # one process per GPU (torchrun): share the host cores between the ranks' planner threads
+        ranks = int(os.environ.get("LOCAL_WORLD_SIZE", "1"))
+        if ranks > 1:
+            try:
+                cores = len(os.sched_getaffinity(0))
+            except AttributeError:
+                cores = os.cpu_count() or 1
+            _ENGINES[device].configure(host_threads=max(2, cores // ranks))
     return _ENGINES[device]
 
 
