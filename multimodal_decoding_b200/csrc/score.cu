@@ -14,7 +14,8 @@
 
 namespace mmd {
 namespace {
-constexpr int THREADS = 288;
+constexpr int THREADS = 576;              // 18 warps: 2 row halves x 9 column groups; one CTA per SM
+constexpr int MT = 5;                     // m-tiles per warp and pass (40 rows)
 constexpr int KC = 16, LDS = KC + 4;
 constexpr int PASS_ROWS = 80;             // 10 m-tiles per pass, two passes cover 152 rows (19 tiles + 1 idle)
 constexpr int RAW_ROW0 = EVAL_PAD;        // first un-standardised imagery row
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
     const double* yhat = prm.yhat + (long)task_id * YHAT_ROWS * Dp;
     const int n_cap = prm.n_cap, n_img = prm.n_img, n_im = prm.n_im;
     const int n_test = n_cap + n_img, n_eval = n_test + n_im;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = (tid >> 5) % 9, wm = (tid >> 5) / 9;
 
     if (tid < 8) cnt_sm[tid] = 0;
     for (int i = tid; i < 160; i += THREADS) nrm_sm[i] = 0.0;
@@ -77,9 +78,9 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
             }
         };
 
-        double acc[10][2][2];
+        double acc[MT][2][2];
 #pragma unroll
-        for (int i = 0; i < 10; ++i)
+        for (int i = 0; i < MT; ++i)
 #pragma unroll
             for (int j = 0; j < 2; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
         double sq = 0.0;                                  // threads 0..159: half a row of the squared norm
@@ -106,13 +107,13 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
                     sq = fma(v.y, v.y, sq);
                 }
             }
-            const double* as = a_st + fr * LDS + fk;
+            const double* as = a_st + (wm * MT * 8 + fr) * LDS + fk;
             const double* bs = Bs + (kc % STAGES) * B_STAGE + (warp * 16 + fr) * LDS + fk;
 #pragma unroll
             for (int k4 = 0; k4 < KC / 4; ++k4) {
                 const double b0 = bs[k4 * 4], b1 = bs[8 * LDS + k4 * 4];
 #pragma unroll
-                for (int i = 0; i < 10; ++i) {
+                for (int i = 0; i < MT; ++i) {
                     const double a = as[i * 8 * LDS + k4 * 4];
                     dmma884(acc[i][0][0], acc[i][0][1], a, b0);
                     dmma884(acc[i][1][0], acc[i][1][1], a, b1);
@@ -128,8 +129,8 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
 
         // ---- distances; first publish each row's own ("same") and cross-modal diagonal entries ----
 #pragma unroll
-        for (int i = 0; i < 10; ++i) {
-            const int gm = row0 + i * 8 + fr;
+        for (int i = 0; i < MT; ++i) {
+            const int gm = row0 + (wm * MT + i) * 8 + fr;
             const double rn = sqrt(nrm_sm[gm < 160 ? gm : 0]);
 #pragma unroll
             for (int j = 0; j < 2; ++j)
@@ -154,8 +155,8 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
         }
         __syncthreads();
 #pragma unroll
-        for (int i = 0; i < 10; ++i) {
-            const int gm = row0 + i * 8 + fr;
+        for (int i = 0; i < MT; ++i) {
+            const int gm = row0 + (wm * MT + i) * 8 + fr;
             if (gm >= M_ROWS) continue;
             const bool is_test = gm < n_test, is_std_im = gm >= n_test && gm < n_eval;
             const bool is_raw_im = gm >= RAW_ROW0 && gm < RAW_ROW0 + n_im;
