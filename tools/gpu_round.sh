@@ -12,10 +12,15 @@ KREG='regex:(factor_solve|predict_kernel|score_kernel|gemm_nt|prep_tasks|pack_tr
 timeout 600 python bench.py $SMALL > gpurun_out/bench_small.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" -c 400 --csv \
    --log-file gpurun_out/launches.csv python bench.py $SMALL > gpurun_out/ncu_launches.log 2>&1
-for kn in factor_solve_kernel predict_kernel score_kernel; do
+for kn in predict_kernel score_kernel; do
   timeout 900 ncu --set full --clock-control none --import-source on -k $kn -s 0 -c 1 -f -o gpurun_out/${kn} \
      python bench.py $SMALL > gpurun_out/ncu_${kn}.log 2>&1
 done
+# factor_solve runs twice per batch: the groups' shared cores (launch 0), then the per-centre launch (launch 1)
+timeout 900 ncu --set full --clock-control none --import-source on -k factor_solve_kernel -s 0 -c 1 -f -o gpurun_out/factor_solve_core \
+     python bench.py $SMALL > gpurun_out/ncu_factor_solve_core.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k factor_solve_kernel -s 1 -c 1 -f -o gpurun_out/factor_solve_kernel \
+     python bench.py $SMALL > gpurun_out/ncu_factor_solve_kernel.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_nt -s 1 -c 1 -f -o gpurun_out/gemm_syrk \
      python bench.py $SMALL > gpurun_out/ncu_gemm.log 2>&1
 ls -la gpurun_out
