@@ -473,11 +473,20 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
     const long ldc = s_p;
     if (jc > 0) {
         // W1 -> the first s_p columns of this centre's W rows (the own panels extend them in place)
-        const int n2 = s_p / 2;
-        for (int e = tid; e < EVAL_PAD * n2; e += THREADS) {
-            const int r = e / n2, c2 = (e % n2) * 2;
-            *reinterpret_cast<double2*>(M + (long)(kp + r) * ld + c2) =
-                *reinterpret_cast<const double2*>(core + (long)(s_p + r) * ldc + c2);
+        // eight independent 16-byte loads in flight per thread (the copy is latency bound otherwise)
+        const int n2 = s_p / 2, total = EVAL_PAD * n2;
+        for (int e0 = tid; e0 < total; e0 += THREADS * 8) {
+            double2 v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * THREADS;
+                if (e < total) v[q] = __ldg(reinterpret_cast<const double2*>(core + (long)(s_p + e / n2) * ldc + (e % n2) * 2));
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int e = e0 + q * THREADS;
+                if (e < total) *reinterpret_cast<double2*>(M + (long)(kp + e / n2) * ld + (e % n2) * 2) = v[q];
+            }
         }
     }
 

@@ -248,3 +248,25 @@ def test_prefix_sharing_group_sizes(engine):
         assert np.abs(got[sample] - want).max() <= TOL, g
         assert np.array_equal(got[sample], want), g
         assert np.abs(got - results[1]).max() <= TOL, g
+
+
+@pytest.mark.parametrize("k,n_dims", [(1500, 768), (250, 1152)])
+def test_neighbourhood_and_feature_sweep(engine, k, n_dims):
+    """BASELINE.json configs[3]: k in {250, 1500} with CLIP (768-d) / SigLIP (1152-d) sized targets and the ~2000
+    training trials of the modality-specific modes; a contiguous patch of centres (so that prefix-sharing groups
+    form) against the oracle."""
+    from multimodal_decoding_b200 import synthetic as syn
+    mesh = syn.make_mesh(level=5, seed=11)                     # 10,242 vertices
+    trials = syn.make_trials(mesh, n_train=2000, n_dims=n_dims, seed=4)
+    inp = syn.make_searchlight_inputs(mesh, trials)
+    _, A = engine.knn(inp.coords, k)
+    patch = A[123][:96]                                        # the 96 vertices nearest to vertex 123
+    engine.upload(inp.X, inp.latents, inp.train_ids, inp.test_ids, inp.imagery_ids, orc.default_is_caption(140))
+    engine.reset_stats()
+    got, flags = engine.searchlight(A[patch], 1.0)
+    assert flags.sum() == 0 and engine.stats()["grouped_centres"] > 48
+    sample = [0, 17, 50, 95]
+    want = orc.search_light(inp.X, inp.latents, A, inp.train_ids, inp.test_ids, inp.imagery_ids, alpha=1.0,
+                            centres=[int(patch[i]) for i in sample])
+    assert np.abs(got[sample] - want).max() <= TOL
+    assert np.array_equal(got[sample], want)
