@@ -1,7 +1,7 @@
 """Throughput of the group-level statistics kernels at fsaverage7 size: TFCE maps/s on the GPU
 next to the numpy/scipy oracle on the host, and the t-map kernel.  Prints one JSON line.
 
-    python tools/bench_group_stats.py [--maps 296] [--cpu-maps 1]
+    python tests/tools/bench_group_stats.py [--maps 296] [--cpu-maps 1]
 """
 import argparse
 import json
@@ -11,7 +11,7 @@ import time
 
 import numpy as np
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from multimodal_decoding_b200 import synthetic as syn  # noqa: E402
 from multimodal_decoding_b200.engine import Engine  # noqa: E402
 from oracle import stats_oracle as so  # noqa: E402  (checker / CPU baseline only)

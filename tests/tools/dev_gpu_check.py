@@ -5,11 +5,11 @@ import time
 
 import numpy as np
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from multimodal_decoding_b200.engine import Engine  # noqa: E402
 from oracle import searchlight_oracle as orc  # noqa: E402
 
-G = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+G = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "golden")
 eng = Engine(0)
 
 g = np.load(os.path.join(G, "knn_small.npz"))

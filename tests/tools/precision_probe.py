@@ -2,7 +2,7 @@
 
 Compares the float64 oracle with fp32-Gram / fp32-Cholesky variants on synthetic smooth betas
 and prints, per variant, how many of the 8 per-centre scores differ and by how much.
-Result summary lives in DESIGN.md §"Precision".  Run: python tools/precision_probe.py [level] [k] [n_centres]
+Result summary lives in DESIGN.md §"Precision".  Run: python tests/tools/precision_probe.py [level] [k] [n_centres]
 """
 import sys
 import time
