@@ -274,12 +274,11 @@ void build_plan(const Rows& rows, int V, const Clustering& cl, int c_begin, int 
     std::atomic<int> next(0);
     auto worker = [&]() {
         std::vector<int> stamp(V, -1);
-        std::vector<int> member_of, grouped, vgen, vcnt;
+        std::vector<int> member_of, grouped, vgen, cur, nxt;
         if (grouping) {
             member_of.assign(n_centres, -1);
             grouped.assign(n_centres, 0);
             vgen.assign(V, -1);
-            vcnt.assign(V, 0);
         }
         int gen = 0;
         for (;;) {
@@ -299,38 +298,46 @@ void build_plan(const Rows& rows, int V, const Clustering& cl, int c_begin, int 
                     cg.order.push_back(s0);
                     const int32_t* row = rows.row(s0);
                     const int scan = std::min(rows.k, 4 * group_size);
-                    for (int j = 1; j < scan && (int)(cg.order.size() - first) < group_size; ++j) {
+                    // The running intersection starts as the seed's neighbourhood; a candidate joins only if the
+                    // per-centre factor/solve cost of the (larger group, smaller core) pair is lower.
+                    cur.clear();
+                    for (int j = 0; j < rows.k; ++j)
+                        if (row[j] >= 0 && row[j] < V) cur.push_back(row[j]);
+                    auto prefix_of = [&](size_t n_core) {
+                        const int sp = std::min((int)(n_core / NB) * NB, kp - NB);
+                        return sp < MIN_SHARED_PREFIX ? 0 : sp;
+                    };
+                    auto cost = [&](int g, int sp) {       // flops per centre up to the (unshared) backward solve
+                        const double k3 = (double)kp * kp * kp, s3 = (double)sp * sp * sp;
+                        const double k2 = (double)kp * kp, s2 = (double)sp * sp;
+                        return (k3 - s3) / 3.0 + s3 / (3.0 * g) + EVAL_PAD * (k2 - s2) + EVAL_PAD * s2 / g;
+                    };
+                    int g = 1, sp = 0;
+                    for (int j = 1; j < scan && g < group_size; ++j) {
                         const int v = row[j];
                         if (v < 0 || v >= V) continue;
                         const int cc = centre_of[v];
-                        if (cc >= 0 && member_of[cc] == c && !grouped[cc] && rows.anchor(cc) == v) {
-                            grouped[cc] = 1;
-                            cg.order.push_back(cc);
-                        }
-                    }
-                    const int g = (int)(cg.order.size() - first);
-                    int sp = 0;
-                    if (g >= 2) {
+                        if (!(cc >= 0 && member_of[cc] == c && !grouped[cc] && rows.anchor(cc) == v)) continue;
                         ++gen;
-                        for (int q = 0; q < g; ++q) {
-                            const int32_t* r = rows.row(cg.order[first + q]);
-                            for (int j = 0; j < rows.k; ++j) {
-                                const int v = r[j];
-                                if (v < 0 || v >= V) continue;
-                                if (vgen[v] != gen) { vgen[v] = gen; vcnt[v] = 1; }
-                                else ++vcnt[v];
-                            }
-                        }
-                        const size_t core0 = cg.core.size();
-                        for (int j = 0; j < rows.k; ++j) {
-                            const int v = row[j];
-                            if (v >= 0 && v < V && vgen[v] == gen && vcnt[v] == g) { cg.core.push_back(v); vcnt[v] = -1; }
-                        }
-                        const int n_core = (int)(cg.core.size() - core0);
-                        sp = std::min(n_core / NB * NB, kp - NB);
-                        if (sp < MIN_SHARED_PREFIX) sp = 0;
-                        std::sort(cg.core.begin() + core0, cg.core.end());
-                        cg.core.resize(core0 + sp);
+                        const int32_t* r = rows.row(cc);
+                        for (int q = 0; q < rows.k; ++q)
+                            if (r[q] >= 0 && r[q] < V) vgen[r[q]] = gen;
+                        nxt.clear();
+                        for (int x : cur)
+                            if (vgen[x] == gen) nxt.push_back(x);
+                        const int sp_new = prefix_of(nxt.size());
+                        if (sp_new == 0 || (g > 1 && cost(g + 1, sp_new) >= cost(g, sp))) continue;
+                        grouped[cc] = 1;
+                        cg.order.push_back(cc);
+                        cur.swap(nxt);
+                        sp = sp_new;
+                        ++g;
+                    }
+                    if (g >= 2) {
+                        std::sort(cur.begin(), cur.end());
+                        cg.core.insert(cg.core.end(), cur.begin(), cur.begin() + sp);
+                    } else {
+                        sp = 0;
                     }
                     cg.size.push_back(g);
                     cg.sp.push_back(sp);

@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(THREADS, 2) predict_kernel(PredictParams prm) 
 #pragma unroll
         for (int j = 0; j < 2; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    const int nk = kp / KC;
+    const int nk = (k + KC - 1) / KC;                  // columns k.. of Zt are zero (padding): skip their chunks
     for (int s = 0; s < STAGES - 1; ++s) {
         if (s < nk) load_stage(s, s);
         cp_async_commit();
