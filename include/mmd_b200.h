@@ -100,7 +100,8 @@ int mmd_searchlight_ragged(mmd_handle* h, const int32_t* indices, const int64_t*
                            int n_centres, double alpha, double* scores_out, int32_t* flags_out);
 
 /* mmd_searchlight plus the null-distribution branch of train_and_test (searchlight.py:61-79): for each of
- * `n_perm` target permutations the fixed predictions are re-scored against permuted targets.
+ * `n_perm` (1..1700 per call; the reference's default is 100) target permutations the fixed predictions are re-scored
+ * against permuted targets.
  *   perm_test     (n_perm x n_test) int32: entry [p][g] is the test trial (position in test_ids order) whose latent
  *                 takes the place of trial g's latent, i.e. `indices` of y_test[indices] (data.py:540-561)
  *   perm_imagery  (n_perm x n_imagery) int32: the same for the imagery latents (the reference draws one of the two

@@ -1136,7 +1136,7 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
     if (!adjacency || !scores_out || !perm_test || !null_out || (h->n_im > 0 && !perm_imagery))
         return fail(h, "mmd_searchlight_null: null pointer");
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight_null");
-    if (n_centres < 0 || n_perm < 1 || n_perm > 8192) return fail(h, "mmd_searchlight_null: bad n_centres / n_perm");
+    if (n_centres < 0 || n_perm < 1 || n_perm > 1700) return fail(h, "mmd_searchlight_null: n_perm must be 1..1700 per call (split larger sets)");
     if (n_centres == 0) return 0;
     const int n_test = h->n_test;
     for (long i = 0; i < (long)n_perm * n_test; ++i)
