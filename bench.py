@@ -4,14 +4,17 @@
 
 Workload (BASELINE.json configs[1]): one synthetic fsaverage7-sized hemisphere (icosphere-7, 163,842 vertices),
 k = 750 nearest neighbours, N_train = 4000, 140 test + 3 imagery trials, D = 1024 (ImageBind), alpha = 1,
-modality-agnostic.  A *step* is one call of the hot path on `--centres-per-step` consecutive centres of the rank's
-vertex shard (successive steps walk through the shard).  `value` is measured with the trial arrays already staged in
-HBM; `e2e` calls the public drop-in `custom_search_light` with HOST buffers every step (pinned X, y, adjacency rows
-in; score dicts out).  With N > 1 (torchrun) every rank works on its own contiguous vertex range ("weak" scaling,
-no data-path collective; the score blocks are all-gathered once per step).
+modality-agnostic.  A *step* is one pass of the hot path over a whole hemisphere (all 163,842 centres; with
+`--centres-per-step` a range of that many consecutive centres).  `value` is measured with the trial arrays already
+staged in HBM (CUDA events on the engine's stream); `e2e` calls the public drop-in `custom_search_light` with HOST
+buffers every step (pinned X, y and the int64 adjacency in; the object array of score dicts out).  With N > 1
+(torchrun) every rank runs its own hemisphere job ("weak" scaling, configs[4] distributes whole searchlights; no
+data-path collective, the score blocks are all-gathered once per step); `--scaling strong` shards ONE hemisphere
+into Morton-ordered vertex ranges instead.
 
-`--impl reference` times the CPU restatement of the reference's per-centre loop (oracle/, float64 numpy/scipy with
-all host threads) on a bounded sample of the same workload.
+`--impl reference` times the CPU restatement of the reference's per-centre loop (oracle/, float64 numpy/scipy) run
+the way the reference runs it -- joblib processes over chunks of centres on all host cores -- on a bounded sample of
+the same workload.
 """
 from __future__ import annotations
 

@@ -270,3 +270,38 @@ def test_neighbourhood_and_feature_sweep(engine, k, n_dims):
                             centres=[int(patch[i]) for i in sample])
     assert np.abs(got[sample] - want).max() <= TOL
     assert np.array_equal(got[sample], want)
+
+
+def test_full_hemisphere_sharing_invariance(engine):
+    """BASELINE.json configs[1] at full size (163,842 vertices, k=750, N_train=4000, D=1024): the score maps with and
+    without prefix sharing (different elimination orders of the same normal equations) agree within the north star's
+    1e-3 on every vertex, and a sample of vertices equals the oracle."""
+    import sys
+    import torch
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    sys_argv, sys.argv = sys.argv, [sys.argv[0]]
+    try:
+        args = bench.parse_args()
+    finally:
+        sys.argv = sys_argv
+    coords, X16, Y16, ids = bench.make_workload(args, torch.device("cuda", engine.device))
+    A = bench.knn_rows(engine, coords, 750, 0, len(coords))
+    engine.upload(X16, Y16, ids[0], ids[1], ids[2], np.arange(140) < 70)
+    try:
+        engine.configure(group_size=1)
+        plain, f0 = engine.searchlight(A, 1.0)
+        engine.configure(group_size=8)
+        engine.reset_stats()
+        shared, f1 = engine.searchlight(A, 1.0)
+        st = engine.stats()
+    finally:
+        engine.configure(group_size=8)
+    assert f0.sum() == 0 and f1.sum() == 0
+    assert st["grouped_centres"] > 0.95 * len(A)
+    assert np.abs(shared - plain).max() <= TOL
+    assert (np.abs(shared - plain).max(axis=1) > 0).mean() < 1e-3      # near-ties at rounding level are rare
+    sample = [0, 40000, 163841]
+    Xh, Yh = X16.cpu().numpy(), Y16.cpu().numpy()
+    want = orc.search_light(Xh, Yh, A, ids[0], ids[1], ids[2], alpha=1.0, centres=sample)
+    assert np.abs(shared[sample] - want).max() <= TOL
