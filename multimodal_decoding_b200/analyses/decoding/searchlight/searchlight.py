@@ -85,10 +85,20 @@ def _is_caption_mask(n_test):
 
 
 def _scores_to_dicts(scores: np.ndarray) -> np.ndarray:
+    """(n, 8) float64 block -> the reference's object array of 8-key dicts (searchlight.py:114, :149).  The cyclic
+    garbage collector is paused while the n dicts are created (they hold only floats)."""
+    import gc
+    from itertools import repeat
     keys = score_keys()
-    out = np.empty(len(scores), dtype=object)
-    for i, row in enumerate(scores):
-        out[i] = dict(zip(keys, row.tolist()))
+    rows = scores.tolist()
+    out = np.empty(len(rows), dtype=object)
+    was_enabled = gc.isenabled()
+    gc.disable()
+    try:
+        out[:] = list(map(dict, map(zip, repeat(keys), rows)))
+    finally:
+        if was_enabled:
+            gc.enable()
     return out
 
 
