@@ -42,6 +42,16 @@ const char* mmd_version(void);
  * with its own CUDA events (bench.py does; the reference only has wall-clock timing, searchlight.py:250-257). */
 void* mmd_stream(mmd_handle* h);
 
+/* Guard mode (set MMD_B200_GUARD=1 in the environment before the library is loaded): every device buffer of the
+ * library carries a 4 KiB band on either side and is pre-filled with 0xA5 bytes.  mmd_check_guards synchronises the
+ * handle's stream and returns the number of buffers whose bands were overwritten since the last call (0 = clean,
+ * always 0 with guard mode off; details on stderr and in mmd_last_error).  Test infrastructure for the GPU pool,
+ * where compute-sanitizer is not available; the reference has no counterpart. */
+int mmd_check_guards(mmd_handle* h);
+/* Proves the detector: writes one byte behind and one byte in front of a scratch buffer and checks that both are
+ * reported.  0 = detector works, -1 = guard mode is off, other = detector failed. */
+int mmd_guard_selftest(mmd_handle* h);
+
 /* Name of score column i (0..7), e.g. "pairwise_acc_captions"; eval.py:9-44 and searchlight.py:87. */
 const char* mmd_score_name(int i);
 

@@ -15,7 +15,7 @@ EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload",
     "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
-    "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels",
+    "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels", "mmd_check_guards", "mmd_guard_selftest",
 ]
 
 _lib = None
@@ -39,6 +39,10 @@ def load():
     lib.mmd_last_error.argtypes = [vp]
     lib.mmd_last_error.restype = C.c_char_p
     lib.mmd_version.restype = C.c_char_p
+    lib.mmd_check_guards.argtypes = [vp]
+    lib.mmd_check_guards.restype = i32
+    lib.mmd_guard_selftest.argtypes = [vp]
+    lib.mmd_guard_selftest.restype = i32
     lib.mmd_stream.argtypes = [vp]
     lib.mmd_stream.restype = vp
     lib.mmd_score_name.argtypes = [i32]

@@ -10,6 +10,7 @@
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <string>
@@ -37,21 +38,64 @@ const char* kScoreNames[MMD_N_SCORES] = {
     "pairwise_acc_imagery_whole_test_set_no_std",
 };
 
+// Guard mode (environment MMD_B200_GUARD=1; compute-sanitizer is not available on the GPU pool): every device
+// buffer gets a 4 KiB band on either side and is filled, bands included, with 0xA5 bytes.  A kernel that writes
+// outside its buffer breaks a band (found when the buffer is released or by mmd_check_guards); a kernel that reads
+// memory nobody wrote sees 0xA5A5... instead of the zeros a fresh cudaMalloc tends to return.
+constexpr size_t GUARD_BYTES = 4096;
+std::atomic<int> g_guard_failures(0);
+bool guard_mode() {
+    static const bool on = [] {
+        const char* e = getenv("MMD_B200_GUARD");
+        return e && *e && *e != '0';
+    }();
+    return on;
+}
+
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
+    void* base = nullptr;       // == p unless guard mode
     cudaError_t ensure(size_t need) {
         if (need <= bytes) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr;
-        bytes = 0;
-        cudaError_t e = cudaMalloc(&p, need);
-        if (e == cudaSuccess) bytes = need;
-        return e;
+        release();
+        const size_t pad = guard_mode() ? GUARD_BYTES : 0;
+        cudaError_t e = cudaMalloc(&base, need + 2 * pad);
+        if (e != cudaSuccess) {
+            base = nullptr;
+            return e;
+        }
+        if (pad && ((e = cudaMemset(base, 0xA5, need + 2 * pad)) != cudaSuccess ||
+                    (e = cudaDeviceSynchronize()) != cudaSuccess))      // the handle's stream does not wait for the null stream
+            return e;
+        p = static_cast<char*>(base) + pad;
+        bytes = need;
+        return cudaSuccess;
+    }
+    // 0 = bands intact (or guard mode off); the device must be idle on this buffer
+    int check() const {
+        if (!p || !guard_mode()) return 0;
+        std::vector<unsigned char> host(2 * GUARD_BYTES);
+        if (cudaMemcpy(host.data(), base, GUARD_BYTES, cudaMemcpyDeviceToHost) != cudaSuccess ||
+            cudaMemcpy(host.data() + GUARD_BYTES, static_cast<char*>(p) + bytes, GUARD_BYTES, cudaMemcpyDeviceToHost) !=
+                cudaSuccess)
+            return 4;
+        int bad = 0;
+        for (size_t i = 0; i < 2 * GUARD_BYTES; ++i)
+            if (host[i] != 0xA5) bad |= i < GUARD_BYTES ? 1 : 2;
+        if (bad) {
+            fprintf(stderr, "mmd_b200 guard: write %s a device buffer of %zu bytes\n",
+                    bad == 3 ? "before and behind" : bad == 1 ? "before" : "behind", bytes);
+            ++g_guard_failures;
+        }
+        return bad;
     }
     void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
+        if (p) {
+            check();
+            cudaFree(base);
+        }
+        p = base = nullptr;
         bytes = 0;
     }
     template <typename T>
@@ -96,6 +140,8 @@ struct mmd_handle {
     DevBuf adj, union_vertices, task_row, task_k, task_core_off, task_core_n, core_work, group_flags, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
+    DevBuf up_x, up_y, up_train, up_eval;   // mmd_upload's staging copies: alive until the packing kernels have run
+    cudaEvent_t up_copied = nullptr;        // recorded behind the last host-to-device copy of mmd_upload
     PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
     DevBuf st_in, st_edges, st_label, st_count, st_out;     // group-level statistics
     DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
@@ -753,6 +799,23 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     return rc;
 }
 
+// every device buffer the handle owns
+std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
+    return {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
+                      &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
+                      &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
+                      &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
+                      &h->pa_sq, &h->pa_count, &h->up_x, &h->up_y, &h->up_train, &h->up_eval};
+}
+
+// the stream must have passed mmd_upload's kernels (any later synchronisation of h->stream will do)
+void release_upload_staging(mmd_handle* h) {
+    h->up_x.release();
+    h->up_y.release();
+    h->up_train.release();
+    h->up_eval.release();
+}
+
 int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double* scores_out, int32_t* flags_out,
                           const char* who, const int64_t* data64 = nullptr) {
     const int n_centres = rows.n;
@@ -770,6 +833,7 @@ int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double*
         CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
+    release_upload_staging(h);
     if (bad == 2) return fail(h, "%s: adjacency holds a vertex index outside [0, %d)", who, h->V);
     if (bad == 1) return fail(h, "internal: neighbour missing from its cluster union");
     return 0;
@@ -806,16 +870,46 @@ void mmd_destroy(mmd_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    DevBuf* bufs[] = {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
-                      &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
-                      &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
-                      &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
-                      &h->pa_sq, &h->pa_count};
+    std::vector<DevBuf*> bufs = handle_buffers(h);
     for (DevBuf* b : bufs) b->release();
+    release_upload_staging(h);
+    if (h->up_copied) cudaEventDestroy(h->up_copied);
     h->adj_host.release();
     for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream);
     delete h;
+}
+
+int mmd_check_guards(mmd_handle* h) {
+    if (!h) return -1;
+    if (!guard_mode()) return 0;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    for (DevBuf* b : handle_buffers(h)) b->check();
+    const int n = g_guard_failures.exchange(0);
+    if (n) fail(h, "mmd_check_guards: %d device buffer(s) were written outside their bounds (details on stderr)", n);
+    return n;
+}
+
+int mmd_guard_selftest(mmd_handle* h) {
+    if (!h) return -1;
+    if (!guard_mode()) return -1;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    DevBuf probe;
+    if (probe.ensure(100) != cudaSuccess) return 2;
+    const int before = g_guard_failures.load();
+    // one byte behind the buffer, then one byte in front of it: both must be reported
+    cudaMemset(static_cast<char*>(probe.p) + probe.bytes, 0, 1);
+    const int behind = probe.check();
+    cudaMemset(static_cast<char*>(probe.p) + probe.bytes, 0xA5, 1);
+    cudaMemset(static_cast<char*>(probe.p) - 1, 0, 1);
+    const int front = probe.check();
+    cudaMemset(static_cast<char*>(probe.p) - 1, 0xA5, 1);
+    const int clean = probe.check();
+    probe.release();
+    g_guard_failures.store(before);
+    return (behind == 2 && front == 1 && clean == 0) ? 0 : 1;
 }
 
 void* mmd_stream(mmd_handle* h) { return h ? (void*)h->stream : nullptr; }
@@ -832,6 +926,10 @@ int mmd_configure(mmd_handle* h, int cluster_size, int batch_centres, int host_t
 
 void mmd_reset_stats(mmd_handle* h) {
     if (!h) return;
+    if (!h->spans.empty()) {                 // mmd_upload leaves its kernels in flight
+        cudaStreamSynchronize(h->stream);
+        resolve_spans(h);
+    }
     memset(h->stage_ms, 0, sizeof(h->stage_ms));
     h->launches = 0;
     h->n_clusters = 0;
@@ -864,6 +962,10 @@ int mmd_set_group_size(mmd_handle* h, int group_size) {
 int mmd_get_stats(mmd_handle* h, float stage_ms[MMD_N_STAGES], int64_t* n_launches, int64_t* n_clusters,
                   double* syrk_flops) {
     if (!h) return 1;
+    if (!h->spans.empty()) {                 // mmd_upload leaves its kernels in flight
+        CU(cudaStreamSynchronize(h->stream));
+        resolve_spans(h);
+    }
     if (stage_ms) memcpy(stage_ms, h->stage_ms, sizeof(h->stage_ms));
     if (n_launches) *n_launches = h->launches;
     if (n_clusters) *n_clusters = h->n_clusters;
@@ -1006,7 +1108,8 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
     for (int i = 0; i < n_imagery; ++i) eval_ids.push_back(imagery_ids[i]);
     const int n_eval = (int)eval_ids.size();
 
-    DevBuf xtmp, ytmp, d_train, d_eval;
+    DevBuf &xtmp = h->up_x, &ytmp = h->up_y, &d_train = h->up_train, &d_eval = h->up_eval;
+    if (!h->up_copied) CU(cudaEventCreateWithFlags(&h->up_copied, cudaEventDisableTiming));
     int rc = 0;
     do {
         const __half* Xd = reinterpret_cast<const __half*>(X);
@@ -1048,6 +1151,7 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
             std::vector<int> iota(EVAL_PAD);
             for (int i = 0; i < EVAL_PAD; ++i) iota[i] = i;
             if ((rc = to_device(h, h->tmp, iota.data(), EVAL_PAD))) break;
+            CUB(cudaEventRecord(h->up_copied, h->stream));      // last read of caller memory
             row_sqnorm_kernel<<<EVAL_PAD, 128, 0, h->stream>>>(h->cand.as<__half>(), h->Dp, h->tmp.as<int>(), EVAL_PAD,
                                                               h->Dp, h->cand_sq.as<double>());
         }
@@ -1055,14 +1159,16 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
         span_end(h, 6);
         CUB(cudaGetLastError());
         if ((rc = run_xty(h))) break;
-        CUB(cudaStreamSynchronize(h->stream));
-        resolve_spans(h);
+        // The caller's buffers are free again once the copies have landed; the XtY contraction (and the staging
+        // copies it reads) stays in flight on the stream, in front of whatever the next call enqueues.
+        CUB(cudaEventSynchronize(h->up_copied));
         h->uploaded = true;
     } while (0);
-    xtmp.release();
-    ytmp.release();
-    d_train.release();
-    d_eval.release();
+    if (rc) {
+        cudaStreamSynchronize(h->stream);
+        resolve_spans(h);
+        release_upload_staging(h);
+    }
     return rc;
 }
 

@@ -7,6 +7,7 @@ device (borrowed).  Nothing here computes on the CPU: every method forwards to l
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -39,6 +40,8 @@ def _ptr(a):
 
 
 class Engine:
+    live = weakref.WeakSet()         # every open engine (the guard-mode check of tests/conftest.py walks it)
+
     def __init__(self, device: int = 0):
         self._lib = _lib.load()
         self._h = C.c_void_p()
@@ -49,6 +52,7 @@ class Engine:
         self.device = int(device)
         self.n_dims = None
         self.n_eval = None
+        Engine.live.add(self)
 
     def close(self):
         if getattr(self, "_h", None):
@@ -265,6 +269,15 @@ class Engine:
     def stream_ptr(self) -> int:
         """cudaStream_t of the handle (wrap with torch.cuda.ExternalStream to record events on it)."""
         return int(self._lib.mmd_stream(self._h) or 0)
+
+    def check_guards(self):
+        """Guard mode (MMD_B200_GUARD=1): raise if a kernel wrote outside one of the library's device buffers."""
+        if getattr(self, "_h", None) and self._lib.mmd_check_guards(self._h) != 0:
+            raise RuntimeError(self._lib.mmd_last_error(self._h).decode())
+
+    def guard_selftest(self) -> int:
+        """0 = guard mode is on and detects a one-byte overrun on either side; -1 = guard mode off."""
+        return int(self._lib.mmd_guard_selftest(self._h))
 
     # -- statistics --------------------------------------------------------------------------
     def reset_stats(self):

@@ -17,3 +17,14 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture(autouse=True)
+def _device_buffer_guards():
+    """With MMD_B200_GUARD=1 (tools/gpu_guard.sh) every test ends with a check of the guard bands around the
+    library's device buffers; a no-op otherwise."""
+    yield
+    if os.environ.get("MMD_B200_GUARD", "0") not in ("", "0"):
+        from multimodal_decoding_b200.engine import Engine
+        for eng in list(Engine.live):
+            eng.check_guards()

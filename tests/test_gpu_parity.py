@@ -305,3 +305,14 @@ def test_full_hemisphere_sharing_invariance(engine):
     Xh, Yh = X16.cpu().numpy(), Y16.cpu().numpy()
     want = orc.search_light(Xh, Yh, A, ids[0], ids[1], ids[2], alpha=1.0, centres=sample)
     assert np.abs(shared[sample] - want).max() <= TOL
+
+
+def test_guard_mode_detector(engine):
+    """tools/gpu_guard.sh runs the suite with MMD_B200_GUARD=1 (guard bands around every device buffer, checked after
+    each test by conftest.py); this proves the detector itself reports a one-byte overrun on either side."""
+    rc = engine.guard_selftest()
+    if os.environ.get("MMD_B200_GUARD", "0") in ("", "0"):
+        assert rc == -1
+        pytest.skip("guard mode is off")
+    assert rc == 0
+    engine.check_guards()
