@@ -79,7 +79,9 @@ int mmd_radius_neighbors(mmd_handle* h, const double* coords, int n_vertices, do
  *   Y            (n_total x n_dims)     float16 row-major, trials x embedding dims
  *   train_ids / test_ids / imagery_ids  row indices into X and Y (searchlight.py:229-232)
  *   test_is_caption[n_test]             1 where TEST_STIM_TYPES == "caption" (data.py:182-187), else 0
- * Builds the vertex-major panels and X_train^T Y_train once (used by every centre). */
+ * Builds the vertex-major panels and X_train^T Y_train once (used by every centre).  Returns once X and Y have been
+ * read; the kernels stay in flight on the handle's stream.  NaN / infinity in X or in the training rows of Y is
+ * recorded here and reported by the searchlight calls (below). */
 int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
                const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
                const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery);
@@ -90,7 +92,10 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
  * the 8 pairwise-accuracy scores (eval.py:126-181).
  *   adjacency    (n_centres x k) int32 vertex ids (columns of X), HOST pointer
  *   scores_out   (n_centres x 8) float64, HOST or DEVICE
- *   flags_out    (n_centres) int32, 1 where the normal matrix was not positive definite; may be NULL */
+ *   flags_out    (n_centres) int32, 1 where the normal matrix was not positive definite; may be NULL
+ * Fails (message starting "Input X contains NaN or infinity" / "Input y ...") when a listed neighbourhood uses a
+ * vertex whose betas are not finite or the training latents are not finite: sklearn's Ridge.fit / predict raise
+ * ValueError on such inputs (check_array; searchlight.py:56-59), and the Python mirror raises ValueError too. */
 int mmd_searchlight(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
                     double* scores_out, int32_t* flags_out);
 

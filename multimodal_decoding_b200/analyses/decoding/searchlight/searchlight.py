@@ -60,6 +60,8 @@ def _estimator_alpha(estimator) -> float:
     alpha = getattr(estimator, "alpha", None)
     if alpha is None or np.ndim(alpha) != 0:
         raise ValueError("estimator must carry a scalar `alpha` (sklearn.linear_model.Ridge)")
+    if not float(alpha) >= 0.0:                        # sklearn: InvalidParameterError (a ValueError) at fit time
+        raise ValueError(f"The 'alpha' parameter of Ridge must be a float in the range [0.0, inf). Got {alpha!r} instead.")
     return float(alpha)
 
 

@@ -140,6 +140,7 @@ struct mmd_handle {
     DevBuf adj, union_vertices, task_row, task_k, task_core_off, task_core_n, core_work, group_flags, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
+    DevBuf vertex_bad, y_bad;               // per vertex: betas hold NaN/inf; one int: training latents hold NaN/inf
     DevBuf up_x, up_y, up_train, up_eval;   // mmd_upload's staging copies: alive until the packing kernels have run
     cudaEvent_t up_copied = nullptr;        // recorded behind the last host-to-device copy of mmd_upload
     PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
@@ -568,7 +569,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     CU(launch_prep_tasks(h->adj.as<int>(), h->task_row.as<long>(), h->task_k.as<int>(), k_max, kp,
                          h->task_union_off.as<long>(), h->task_union_n.as<int>(), h->union_vertices.as<int>(),
                          h->task_core_off.as<long>(), h->task_core_n.as<int>(), h->V,
-                         n_all, h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
+                         h->vertex_bad.as<unsigned char>(), n_all, h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
     span_end(h);
 
     span_begin(h, ST_SYRK);
@@ -799,13 +800,23 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     return rc;
 }
 
+// The device-side checks of a searchlight call (prep_tasks_kernel's flag word, the latents' flag of mmd_upload).
+int report_input_flags(mmd_handle* h, int bad, int y_bad, const char* who) {
+    if (bad & 2) return fail(h, "%s: adjacency holds a vertex index outside [0, %d)", who, h->V);
+    // sklearn's Ridge.fit / predict validate their inputs (check_array) and raise ValueError
+    if (bad & 4) return fail(h, "Input X contains NaN or infinity (%s: a neighbourhood uses a vertex whose betas are not finite)", who);
+    if (y_bad) return fail(h, "Input y contains NaN or infinity (%s: training latents must be finite)", who);
+    if (bad & 1) return fail(h, "internal: neighbour missing from its cluster union");
+    return 0;
+}
+
 // every device buffer the handle owns
 std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
     return {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
                       &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
                       &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
-                      &h->pa_sq, &h->pa_count, &h->up_x, &h->up_y, &h->up_train, &h->up_eval};
+                      &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval};
 }
 
 // the stream must have passed mmd_upload's kernels (any later synchronisation of h->stream will do)
@@ -825,8 +836,9 @@ int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double*
         h->events_used = 0;
         return 1;
     }
-    int bad = 0;
+    int bad = 0, y_bad = 0;
     CU(cudaMemcpyAsync(&bad, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(&y_bad, h->y_bad.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaMemcpyAsync(scores_out, h->scores.p, (size_t)n_centres * MMD_N_SCORES * sizeof(double), cudaMemcpyDefault,
                        h->stream));
     if (flags_out)
@@ -834,9 +846,7 @@ int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double*
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
     release_upload_staging(h);
-    if (bad == 2) return fail(h, "%s: adjacency holds a vertex index outside [0, %d)", who, h->V);
-    if (bad == 1) return fail(h, "internal: neighbour missing from its cluster union");
-    return 0;
+    return report_input_flags(h, bad, y_bad, who);
 }
 
 }  // namespace
@@ -1140,10 +1150,17 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
         CUB(h->cand_sq.ensure((size_t)EVAL_PAD * sizeof(double)));
         CUB(h->XtY.ensure((size_t)n_vertices * h->Dp * sizeof(double)));
         CUB(cudaMemsetAsync(h->Yt.p, 0, (size_t)h->Dp * h->ldt * sizeof(__half), h->stream));
+        CUB(h->vertex_bad.ensure((size_t)n_vertices));
+        CUB(h->y_bad.ensure(sizeof(int)));
+        CUB(cudaMemsetAsync(h->vertex_bad.p, 0, (size_t)n_vertices, h->stream));
+        CUB(cudaMemsetAsync(h->y_bad.p, 0, sizeof(int), h->stream));
         span_begin(h, ST_PACK);
-        launch_pack_transpose(Xd, n_vertices, d_train.as<int>(), n_train, n_vertices, h->Xt.as<__half>(), h->ldt, h->stream);
-        launch_pack_transpose(Xd, n_vertices, d_eval.as<int>(), n_eval, n_vertices, h->Xe.as<__half>(), EVAL_PAD, h->stream);
-        launch_pack_transpose(Yd, n_dims, d_train.as<int>(), n_train, n_dims, h->Yt.as<__half>(), h->ldt, h->stream);
+        launch_pack_transpose(Xd, n_vertices, d_train.as<int>(), n_train, n_vertices, h->Xt.as<__half>(), h->ldt,
+                              h->vertex_bad.as<unsigned char>(), nullptr, h->stream);
+        launch_pack_transpose(Xd, n_vertices, d_eval.as<int>(), n_eval, n_vertices, h->Xe.as<__half>(), EVAL_PAD,
+                              h->vertex_bad.as<unsigned char>(), nullptr, h->stream);
+        launch_pack_transpose(Yd, n_dims, d_train.as<int>(), n_train, n_dims, h->Yt.as<__half>(), h->ldt, nullptr,
+                              h->y_bad.as<int>(), h->stream);
         gather_rows_f16_kernel<<<EVAL_PAD, 256, 0, h->stream>>>(Yd, n_dims, d_eval.as<int>(), n_eval, n_dims,
                                                                h->cand.as<__half>(), EVAL_PAD, h->Dp);
         // squared norms of the candidate rows (identity row list = first EVAL_PAD entries of an iota)
@@ -1267,16 +1284,15 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
         h->events_used = 0;
         return 1;
     }
-    int bad = 0;
+    int bad = 0, y_bad = 0;
     CU(cudaMemcpyAsync(&bad, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(&y_bad, h->y_bad.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaMemcpyAsync(scores_out, h->scores.p, (size_t)n_centres * MMD_N_SCORES * sizeof(double), cudaMemcpyDefault, h->stream));
     CU(cudaMemcpyAsync(null_out, h->null_out.p, (size_t)n_centres * n_perm * 6 * sizeof(double), cudaMemcpyDefault, h->stream));
     if (flags_out) CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
-    if (bad == 2) return fail(h, "mmd_searchlight_null: adjacency holds a vertex index outside [0, %d)", h->V);
-    if (bad == 1) return fail(h, "internal: neighbour missing from its cluster union");
-    return 0;
+    return report_input_flags(h, bad, y_bad, "mmd_searchlight_null");
 }
 
 // ---- eval.py primitives on arbitrary shapes (host float64 buffers) ----

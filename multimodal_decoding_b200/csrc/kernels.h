@@ -9,7 +9,7 @@ namespace mmd {
 
 // ---- pack.cu -----------------------------------------------------------------------------
 void launch_pack_transpose(const __half* X, long ldx, const int* ids_dev, int n_ids, int V, __half* out,
-                           int ld_out, cudaStream_t s);
+                           int ld_out, unsigned char* bad_row, int* any_bad, cudaStream_t s);
 __global__ void row_sqnorm_kernel(const __half* Y, long ldy, const int* rows, int n_rows, int D, double* sq);
 __global__ void half_to_double_kernel(const __half* in, double* out, long n);
 
@@ -128,8 +128,8 @@ cudaError_t launch_pairwise_count(const double* dist, int r, int c, unsigned lon
 cudaError_t launch_prep_tasks(const int* adjacency, const long* task_row_off, const int* task_k, int k_max, int kp_max,
                               const long* task_union_off, const int* task_union_n, const int* union_vertices,
                               const long* task_core_off, const int* task_core_n,
-                              int n_vertices, int n_tasks, int* nbr_sorted, int* loc, int* bad_index_flag,
-                              cudaStream_t s);
+                              int n_vertices, const unsigned char* vertex_bad, int n_tasks, int* nbr_sorted, int* loc,
+                              int* bad_index_flag, cudaStream_t s);
 __global__ void gather_rows_f16_kernel(const __half* Y, long ldy, const int* rows, int n_rows, int D, __half* out,
                                        int n_out, int ld_out);
 

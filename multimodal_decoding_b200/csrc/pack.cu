@@ -10,16 +10,26 @@
 namespace mmd {
 
 // out[v][n] = X[ids[n]][v]  (n < n_ids), 0 for n_ids <= n < ld_out.   64 x 64 tiles through shared memory.
+// A NaN or infinite input marks its output row (`bad_row[v] = 1`) and/or sets `*any_bad`: sklearn's Ridge refuses
+// such inputs (`check_array`, ValueError) and the searchlight reports it for the centres that use the vertex.
 __global__ void __launch_bounds__(256) pack_transpose_kernel(const __half* __restrict__ X, long ldx,
                                                              const int* __restrict__ ids, int n_ids, int V,
-                                                             __half* __restrict__ out, int ld_out) {
+                                                             __half* __restrict__ out, int ld_out,
+                                                             unsigned char* __restrict__ bad_row,
+                                                             int* __restrict__ any_bad) {
     __shared__ __half tile[64][66];
     const int v0 = blockIdx.x * 64, n0 = blockIdx.y * 64;
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;   // 64 x 4
     for (int r = ty; r < 64; r += 4) {
         int n = n0 + r, v = v0 + tx;
         __half val = __float2half(0.f);
-        if (n < n_ids && v < V) val = X[(long)ids[n] * ldx + v];
+        if (n < n_ids && v < V) {
+            val = X[(long)ids[n] * ldx + v];
+            if ((__half_as_ushort(val) & 0x7c00u) == 0x7c00u) {      // exponent all ones: NaN or infinity
+                if (bad_row) bad_row[v] = 1;
+                if (any_bad) *any_bad = 1;
+            }
+        }
         tile[r][tx] = val;
     }
     __syncthreads();
@@ -30,9 +40,9 @@ __global__ void __launch_bounds__(256) pack_transpose_kernel(const __half* __res
 }
 
 void launch_pack_transpose(const __half* X, long ldx, const int* ids_dev, int n_ids, int V, __half* out,
-                           int ld_out, cudaStream_t s) {
+                           int ld_out, unsigned char* bad_row, int* any_bad, cudaStream_t s) {
     dim3 grid((V + 63) / 64, (ld_out + 63) / 64);
-    pack_transpose_kernel<<<grid, 256, 0, s>>>(X, ldx, ids_dev, n_ids, V, out, ld_out);
+    pack_transpose_kernel<<<grid, 256, 0, s>>>(X, ldx, ids_dev, n_ids, V, out, ld_out, bad_row, any_bad);
 }
 
 // sq[j] = sum_d Y[rows[j]][d]^2 in float64 (candidate norms for the cosine distances)

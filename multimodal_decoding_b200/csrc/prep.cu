@@ -16,6 +16,7 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
                                                          const int* __restrict__ union_vertices,
                                                          const long* __restrict__ task_core_off,
                                                          const int* __restrict__ task_core_n, int n_vertices,
+                                                         const unsigned char* __restrict__ vertex_bad,
                                                          int* __restrict__ nbr_sorted, int* __restrict__ loc,
                                                          int* __restrict__ bad_index_flag) {
     extern __shared__ int sm[];                 // next power of two >= the largest k of the launch
@@ -27,8 +28,10 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
     for (int i = tid; i < np2; i += blockDim.x) {
         int v = i < k ? row[i] : 0x7fffffff;
         if (i < k && (v < 0 || v >= n_vertices)) {
-            atomicMax(bad_index_flag, 2);       // 2 = vertex id out of range (wins over 1)
+            atomicOr(bad_index_flag, 2);        // bit 1 = vertex id out of range
             v = 0;
+        } else if (i < k && vertex_bad[v]) {
+            atomicOr(bad_index_flag, 4);        // bit 2 = a neighbour's betas hold NaN or infinity
         }
         sm[i] = v;
     }
@@ -73,7 +76,7 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
                 else hi = mid;
             }
             pos = lo;
-            if (lo >= un || uni[lo] != v) atomicMax(bad_index_flag, 1);   // 1 = not in the union
+            if (lo >= un || uni[lo] != v) atomicOr(bad_index_flag, 1);    // bit 0 = not in the union
         }
         nbr_sorted[(long)t * kp + dst] = v;
         loc[(long)t * kp + dst] = pos;
@@ -83,13 +86,13 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
 cudaError_t launch_prep_tasks(const int* adjacency, const long* task_row_off, const int* task_k, int k_max, int kp_max,
                               const long* task_union_off, const int* task_union_n, const int* union_vertices,
                               const long* task_core_off, const int* task_core_n,
-                              int n_vertices, int n_tasks, int* nbr_sorted, int* loc, int* bad_index_flag,
-                              cudaStream_t s) {
+                              int n_vertices, const unsigned char* vertex_bad, int n_tasks, int* nbr_sorted, int* loc,
+                              int* bad_index_flag, cudaStream_t s) {
     int np2 = 1;
     while (np2 < k_max) np2 <<= 1;
     prep_tasks_kernel<<<n_tasks, 256, np2 * sizeof(int), s>>>(adjacency, task_row_off, task_k, kp_max, task_union_off,
                                                              task_union_n, union_vertices, task_core_off, task_core_n,
-                                                             n_vertices, nbr_sorted, loc, bad_index_flag);
+                                                             n_vertices, vertex_bad, nbr_sorted, loc, bad_index_flag);
     return cudaGetLastError();
 }
 

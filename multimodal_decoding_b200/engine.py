@@ -67,7 +67,9 @@ class Engine:
 
     def _check(self, rc):
         if rc != 0:
-            raise RuntimeError(self._lib.mmd_last_error(self._h).decode())
+            msg = self._lib.mmd_last_error(self._h).decode()
+            # sklearn's input validation (Ridge.fit / predict -> check_array) raises ValueError for NaN / infinity
+            raise ValueError(msg) if msg.startswith("Input ") else RuntimeError(msg)
 
     def configure(self, cluster_size=0, batch_centres=0, host_threads=0, group_size=0):
         self._check(self._lib.mmd_configure(self._h, cluster_size, batch_centres, host_threads))

@@ -37,6 +37,33 @@ def test_engine_fails_loudly_without_gpu():
         raise AssertionError("Engine(0) must raise without a CUDA device")
 
 
+def test_estimator_protocol_and_score_dicts():
+    """Host logic of the drop-in: the loop only accepts what searchlight.py:240 builds (Ridge(alpha,
+    fit_intercept=False)) and hands back the reference's object array of 8-key dicts (searchlight.py:114, :149)."""
+    import pytest
+    from sklearn.linear_model import Ridge
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+    from multimodal_decoding_b200.engine import score_keys
+    assert sl._estimator_alpha(Ridge(alpha=3, fit_intercept=False)) == 3.0
+    assert sl._estimator_alpha(Ridge(alpha=0.0, fit_intercept=False)) == 0.0
+    for bad in (Ridge(alpha=1.0), Ridge(alpha=-1.0, fit_intercept=False),
+                Ridge(alpha=np.ones(4), fit_intercept=False), object()):
+        with pytest.raises(ValueError):
+            sl._estimator_alpha(bad)
+    with pytest.raises(TypeError, match="float16"):
+        sl._as_f16(np.zeros((3, 3), dtype=np.float32), "X")
+    block = np.random.default_rng(0).random((5, 8))
+    out = sl._scores_to_dicts(block)
+    assert out.shape == (5,) and out.dtype == object
+    assert list(out[2].keys()) == list(score_keys()) and [out[2][k] for k in score_keys()] == block[2].tolist()
+    assert all(type(v) is float for v in out[0].values())
+    assert sl._scores_to_dicts(np.zeros((0, 8))).shape == (0,)
+    # ragged (radius-mode) adjacency is told apart from the rectangular k-NN matrix
+    assert sl._is_ragged([np.arange(3), np.arange(5)]) and not sl._is_ragged(np.zeros((4, 3), dtype=np.int64))
+    assert isinstance(sl._rectangular([np.arange(3), np.arange(3)]), np.ndarray)
+    assert isinstance(sl._rectangular([np.arange(3), np.arange(5)]), list)
+
+
 def test_split_bounds_equals_array_split():
     from multimodal_decoding_b200.sharding import split_bounds, spatial_order
     for n, parts in ((163842, 8), (10, 3), (7, 7), (5, 8)):

@@ -160,6 +160,40 @@ def test_errors(engine, golden_dir):
     assert scores.shape == (0, 8)
 
 
+def test_non_finite_inputs_raise_like_sklearn(engine, golden_dir):
+    """Ridge.fit / predict validate their inputs (sklearn check_array): NaN or infinity in the betas of a centre's
+    neighbourhood (training, test or imagery trials) or in the training latents is a ValueError in the reference
+    (searchlight.py:56-59).  Centres that do not touch the vertex are unaffected; NaN in *test* latents is no error
+    there either (cdist just propagates it)."""
+    g = np.load(os.path.join(golden_dir, "searchlight_small.npz"))
+    tr, te, im = _ids(g)
+    is_cap = orc.default_is_caption(len(te))
+    A = g["adjacency"]
+    vertex = int(A[0, 3])
+    uses = np.array([vertex in row for row in A])
+    assert uses.any() and not uses.all()
+    for trial, value in ((int(tr[7]), np.nan), (int(te[2]), np.inf), (int(im[0]), -np.inf)):
+        X = g["X"].copy()
+        X[trial, vertex] = value
+        engine.upload(X, g["latents"], tr, te, im, is_cap)
+        with pytest.raises(ValueError, match="Input X contains NaN or infinity"):
+            engine.searchlight(A[uses][:5], 1.0)
+        clean, flags = engine.searchlight(A[~uses], 1.0)
+        assert flags.sum() == 0 and np.abs(clean - g["scores"][~uses]).max() <= TOL
+    Y = g["latents"].copy()
+    Y[int(tr[3]), 5] = np.nan
+    engine.upload(g["X"], Y, tr, te, im, is_cap)
+    with pytest.raises(ValueError, match="Input y contains NaN or infinity"):
+        engine.searchlight(A[:4], 1.0)
+    Y = g["latents"].copy()
+    Y[int(te[3]), 5] = np.nan                       # test latents: no validation in the reference
+    engine.upload(g["X"], Y, tr, te, im, is_cap)
+    engine.searchlight(A[:4], 1.0)
+    engine.upload(g["X"], g["latents"], tr, te, im, is_cap)
+    ok, _ = engine.searchlight(A[:4], 1.0)
+    assert np.abs(ok - g["scores"][:4]).max() <= TOL
+
+
 # ---- radius mode: ragged neighbourhoods (searchlight.py:164-171) ---------------------------------------------
 def _ragged(g):
     off = g["offsets"]
