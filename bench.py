@@ -206,7 +206,7 @@ def cpu_centres_per_sec(X, Y, A_rows, ids, n_centres, budget_s=30.0):
 # divided by the batch's centres): profiles/r1_*_v5_details.csv, captured with tools/gpu_round.sh and
 # tools/gpu_capture_fs.sh at config 2.  factor_solve = the per-centre launch (23.6 MB) + the shared-core launch (1.7 MB).
 NCU_DRAM_BYTES_PER_CENTRE = {"factor_solve": 23.8e6, "predict": 2.19e6, "score": 1.32e6, "syrk": 0.08e6}
-FP64_TENSOR_PEAK_TFLOPS = 37.1      # DMMA m8n8k4, measured on this pool with tools/peak_probe.cu (gpurun_out_peaks.log)
+FP64_TENSOR_PEAK_TFLOPS = 37.1      # DMMA m8n8k4, measured on this pool with tools/peak_probe.cu (profiles/r1_measured_peaks_fp64.log)
 
 
 def load_peaks():
