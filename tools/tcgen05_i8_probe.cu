@@ -19,8 +19,8 @@
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("{\"error\": \"%s at line %d\"}\n", cudaGetErrorString(e), __LINE__); return 1; } } while (0)
 
-constexpr int M = 128, N = 256, K = 256;
-constexpr int A_BYTES = M * K, B_BYTES = N * K;
+constexpr int M = 128, K = 256;
+constexpr int A_BYTES = M * K;
 constexpr int TMEM_COLS = 256;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -32,19 +32,33 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo_bytes,
 }
 
 // repeats: how often the whole K loop is issued (1 for the correctness run; accumulates on after the first MMA)
+// A_MN: A is given as (K x M) with M contiguous -- the form a gathered row of XtY slices has -- and staged in the
+// MN-major canonical layout  offset(m, k) = (m / 16) * (K * 16) + (k / 8) * 128 + (k % 8) * 16 + m % 16
+// (SBO = K * 16 between 16-byte m-chunks, LBO = 128 between blocks of 8 k); one MMA (K = 32) spans four k-blocks.
+template <int N, bool A_MN>
 __global__ void __launch_bounds__(128, 1) i8_tile_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ B,
                                                          int32_t* __restrict__ C, int repeats, int* __restrict__ status) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* As = smem;
     uint8_t* Bs = smem + A_BYTES;
+    constexpr int B_BYTES = N * K;
+    (void)B_BYTES;
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_base_sm;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     // global (row-major, K contiguous) -> canonical layout, 16 bytes at a time
-    for (int i = tid; i < M * (K / 16); i += 128) {
-        const int r = i / (K / 16), j = i % (K / 16);
-        *reinterpret_cast<int4*>(As + j * (M * 16) + r * 16) = *reinterpret_cast<const int4*>(A + (size_t)r * K + j * 16);
+    if (A_MN) {
+        for (int i = tid; i < K * (M / 16); i += 128) {
+            const int k = i / (M / 16), mc = i % (M / 16);
+            *reinterpret_cast<int4*>(As + mc * (K * 16) + (k / 8) * 128 + (k % 8) * 16) =
+                *reinterpret_cast<const int4*>(A + (size_t)k * M + mc * 16);
+        }
+    } else {
+        for (int i = tid; i < M * (K / 16); i += 128) {
+            const int r = i / (K / 16), j = i % (K / 16);
+            *reinterpret_cast<int4*>(As + j * (M * 16) + r * 16) = *reinterpret_cast<const int4*>(A + (size_t)r * K + j * 16);
+        }
     }
     for (int i = tid; i < N * (K / 16); i += 128) {
         const int r = i / (K / 16), j = i % (K / 16);
@@ -66,12 +80,13 @@ __global__ void __launch_bounds__(128, 1) i8_tile_kernel(const int8_t* __restric
 
     if (tid == 0) {
         // instruction descriptor: D = S32, A = B = signed 8 bit, both K-major, N >> 3, M >> 4
-        const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+        const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((uint32_t)(N >> 3) << 17) |
+                               ((uint32_t)(M >> 4) << 24);
         const uint32_t a0 = smem_u32(As), b0 = smem_u32(Bs);
         for (int rep = 0; rep < repeats; ++rep) {
 #pragma unroll 1
             for (int ks = 0; ks < K / 32; ++ks) {
-                const uint64_t adesc = make_desc(a0 + ks * 2 * (M * 16), M * 16, 128);
+                const uint64_t adesc = A_MN ? make_desc(a0 + ks * 4 * 128, 128, K * 16) : make_desc(a0 + ks * 2 * (M * 16), M * 16, 128);
                 const uint64_t bdesc = make_desc(b0 + ks * 2 * (N * 16), N * 16, 128);
                 const uint32_t accumulate = (rep | ks) != 0;
                 asm volatile(
@@ -103,22 +118,19 @@ __global__ void __launch_bounds__(128, 1) i8_tile_kernel(const int8_t* __restric
 
     if (done && C != nullptr) {
         // warp w owns TMEM lanes 32w .. 32w+31 = rows of the tile; 32 columns per load
-        for (int c0 = 0; c0 < N; c0 += 32) {
-            uint32_t v[32];
+        for (int c0 = 0; c0 < N; c0 += 16) {
+            uint32_t v[16];
             const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + c0;
             asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-                  "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-                  "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-                  "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                  "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                 : "r"(taddr));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             int32_t* crow = C + ((size_t)blockIdx.x * M + warp * 32 + lane) * N + c0;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) crow[j] = (int32_t)v[j];
+            for (int j = 0; j < 16; ++j) crow[j] = (int32_t)v[j];
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -127,11 +139,11 @@ __global__ void __launch_bounds__(128, 1) i8_tile_kernel(const int8_t* __restric
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
 }
 
-int main() {
-    cudaDeviceProp p;
-    CK(cudaGetDeviceProperties(&p, 0));
+template <int N, bool A_MN>
+int run_case(const cudaDeviceProp& p, const char* name) {
     const int sms = p.multiProcessorCount;
-    std::vector<int8_t> hA(A_BYTES), hB(B_BYTES);
+    constexpr int B_BYTES = N * K;
+    std::vector<int8_t> hA(A_BYTES), hB(B_BYTES);      // A: (M x K) K contiguous, or (K x M) M contiguous when A_MN
     srand(7);
     for (auto& v : hA) v = (int8_t)(rand() % 129 - 64);
     for (auto& v : hB) v = (int8_t)(rand() % 129 - 64);
@@ -147,9 +159,9 @@ int main() {
     CK(cudaMemset(dC, 0xff, sizeof(int32_t) * M * N));
     CK(cudaMemset(dstatus, 0, sizeof(int)));
     const int smem_bytes = A_BYTES + B_BYTES;
-    CK(cudaFuncSetAttribute(i8_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    CK(cudaFuncSetAttribute(i8_tile_kernel<N, A_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
 
-    i8_tile_kernel<<<1, 128, smem_bytes>>>(dA, dB, dC, 1, dstatus);
+    i8_tile_kernel<N, A_MN><<<1, 128, smem_bytes>>>(dA, dB, dC, 1, dstatus);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     int status = 0;
@@ -160,26 +172,27 @@ int main() {
     for (int i = 0; i < M; ++i)
         for (int j = 0; j < N; ++j) {
             int32_t want = 0;
-            for (int k = 0; k < K; ++k) want += (int32_t)hA[(size_t)i * K + k] * (int32_t)hB[(size_t)j * K + k];
+            for (int k = 0; k < K; ++k)
+                want += (int32_t)(A_MN ? hA[(size_t)k * M + i] : hA[(size_t)i * K + k]) * (int32_t)hB[(size_t)j * K + k];
             if (want != hC[(size_t)i * N + j]) {
                 if (first < 0) first = (long)i * N + j;
                 ++mismatches;
             }
         }
-    printf("{\"gpu\": \"%s\", \"tile\": \"%dx%dx%d s8 -> s32\", \"status\": %d, \"mismatches\": %ld, \"first_mismatch\": %ld",
-           p.name, M, N, K, status, mismatches, first);
+    printf("{\"case\": \"%s\", \"gpu\": \"%s\", \"tile\": \"%dx%dx%d s8 -> s32\", \"status\": %d, \"mismatches\": %ld, \"first_mismatch\": %ld",
+           name, p.name, M, N, K, status, mismatches, first);
     if (status == 0 && mismatches == 0) {
         // throughput: one CTA per SM, the K loop issued `reps` times from resident shared memory
         const int reps = 2000;
         cudaEvent_t e0, e1;
         cudaEventCreate(&e0);
         cudaEventCreate(&e1);
-        i8_tile_kernel<<<sms, 128, smem_bytes>>>(dA, dB, nullptr, reps, dstatus);
+        i8_tile_kernel<N, A_MN><<<sms, 128, smem_bytes>>>(dA, dB, nullptr, reps, dstatus);
         CK(cudaDeviceSynchronize());
         float best = 1e30f;
         for (int r = 0; r < 3; ++r) {
             cudaEventRecord(e0);
-            i8_tile_kernel<<<sms, 128, smem_bytes>>>(dA, dB, nullptr, reps, dstatus);
+            i8_tile_kernel<N, A_MN><<<sms, 128, smem_bytes>>>(dA, dB, nullptr, reps, dstatus);
             cudaEventRecord(e1);
             CK(cudaEventSynchronize(e1));
             float ms;
@@ -190,5 +203,15 @@ int main() {
         printf(", \"timed_status\": %d, \"tcgen05_i8_tops\": %.1f", status, 2.0 * M * N * K * (double)reps * sms / best * 1e-9);
     }
     printf("}\n");
+    cudaFree(dA); cudaFree(dB); cudaFree(dC); cudaFree(dstatus);
+    return 0;
+}
+
+int main() {
+    cudaDeviceProp p;
+    CK(cudaGetDeviceProperties(&p, 0));
+    if (run_case<256, false>(p, "A K-major, N=256")) return 1;
+    if (run_case<144, false>(p, "A K-major, N=144 (one eval block)")) return 1;
+    if (run_case<144, true>(p, "A MN-major (gathered rows), N=144")) return 1;
     return 0;
 }
