@@ -203,9 +203,9 @@ def cpu_centres_per_sec(X, Y, A_rows, ids, n_centres, budget_s=30.0):
 # roofline bookkeeping
 # ----------------------------------------------------------------------------------------------------------
 # DRAM bytes per centre (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of a full batch,
-# divided by the batch's centres): profiles/r1_*_v5_details.csv, captured with tools/gpu_round.sh and
+# divided by the batch's centres): profiles/r1_*_v6_details.csv, captured with tools/gpu_round.sh and
 # tools/gpu_capture_fs.sh at config 2.  factor_solve = the per-centre launch (23.6 MB) + the shared-core launch (1.7 MB).
-NCU_DRAM_BYTES_PER_CENTRE = {"factor_solve": 23.8e6, "predict": 2.19e6, "score": 1.32e6, "syrk": 0.08e6}
+NCU_DRAM_BYTES_PER_CENTRE = {"factor_solve": 25.3e6, "predict": 2.22e6, "score": 1.32e6, "syrk": 0.09e6}
 FP64_TENSOR_PEAK_TFLOPS = 37.1      # DMMA m8n8k4, measured on this pool with tools/peak_probe.cu (profiles/r1_measured_peaks_fp64.log)
 
 
@@ -246,7 +246,7 @@ def roofline_entry(stats, n_centres, args, peaks):
     out = {"kernel": top, "stage_ms": {s: round(ms[s], 3) for s in per_centre}, "stage_share": shares,
            "launches_of_kernel": n_batches, "avg_launch_ms": round(ms[top] / n_batches, 3),
            "traffic_source": "ncu --set full of one full batch, bytes per centre x centres per launch "
-                             "(profiles/r1_*_v5_details.csv)" if traffic else None}
+                             "(profiles/r1_*_v6_details.csv)" if traffic else None}
     if top in ("syrk", "factor_solve", "predict"):
         executed = (stats["syrk_flops"] if top == "syrk" else stats["solve_flops"] if top == "factor_solve"
                     else stage_flops_per_centre(top, k, ntr, 144, D) * n_centres)

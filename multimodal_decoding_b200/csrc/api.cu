@@ -149,7 +149,7 @@ struct mmd_handle {
     int n_perm = 0;
     std::vector<int> int_of_test;   // position in test_ids order -> internal evaluation row (captions first)
     // knobs
-    int cluster_size = 256, batch_centres = 2048, host_threads = 0, group_size = 8;
+    int cluster_size = 256, batch_centres = 6144, host_threads = 0, group_size = 8;
     // stats
     float stage_ms[MMD_N_STAGES] = {0};
     int64_t launches = 0, n_clusters = 0, n_batches = 0, n_core_tasks = 0, n_grouped = 0, sum_sp = 0, plan_us = 0,
@@ -652,7 +652,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
 
 // One chunk of clusters: upload its unions and shared cores, size the workspaces, run its batches.
 int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, int k_max, int kp, double alpha,
-              bool with_null, bool raw_yhat) {
+              bool with_null, bool raw_yhat, int batch_cap) {
     const int n_clusters = (int)plan.cl_off.size() - 1;
     if (to_device(h, h->union_vertices, plan.un_vert.data(), plan.un_vert.size())) return 1;
     if (plan.core_vert.size() > total / 2) return fail(h, "internal: shared cores exceed their bound");
@@ -668,7 +668,11 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
         }
     }
 
-    // batches: whole clusters, at most batch_centres centres
+    // batches: whole clusters, at most batch_cap centres (a cluster may overshoot), the chunk split evenly so that no
+    // small remainder batch runs with the GPU half empty
+    const int chunk_tasks = plan.cl_off[n_clusters];
+    const int n_batches = std::max(1, (chunk_tasks + batch_cap - 1) / batch_cap);
+    const int batch_target = (chunk_tasks + n_batches - 1) / n_batches;
     std::vector<int> batch_start(1, 0);
     size_t max_pool = 0, cur_pool = 0;
     int cur_tasks = 0, max_tasks = 0, cur_core = 0, max_core = 0;
@@ -678,7 +682,7 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
         for (int g = plan.cl_grp_off[c]; g < plan.cl_grp_off[c + 1]; ++g) n_core_c += plan.grp_sp[g] > 0;
         const size_t u = (size_t)(plan.un_off[c + 1] - plan.un_off[c]);
         const size_t g = u * round_up((int)u, 8);
-        if (cur_tasks > 0 && cur_tasks + m > h->batch_centres) {
+        if (cur_tasks > 0 && (cur_tasks + m > batch_cap || cur_tasks + m / 2 > batch_target)) {
             batch_start.push_back(c);
             cur_tasks = 0;
             cur_pool = 0;
@@ -758,6 +762,24 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     h->adj_h2d_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_stage0).count();
     const int kp = round_up(k_max, NB);
 
+    // Centres per batch: the configured size, capped so that the per-centre workspaces (factor + solve panel, shared
+    // cores, predictions, index lists, a share of the cluster Grams) take at most half of the device memory that is
+    // free, counting what the handle already holds.
+    int batch_cap = h->batch_centres;
+    {
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+            const size_t held = h->work.bytes + h->yhat.bytes + h->core_work.bytes + h->nbr_sorted.bytes + h->loc.bytes +
+                                h->dist.bytes + h->gram_pool.bytes;
+            const double per_centre = 1.25 * (double)(kp + EVAL_PAD) * kp * sizeof(double) +
+                                      (double)YHAT_ROWS * h->Dp * sizeof(double) + 2.5 * kp * sizeof(int) +
+                                      0.1 * (double)kp * kp * sizeof(double) +
+                                      (with_null ? (double)NULL_DIST_ROWS * EVAL_PAD * sizeof(double) : 0.0);
+            const double fit = 0.5 * ((double)free_b + (double)held) / per_centre;
+            batch_cap = (int)std::max(256.0, std::min((double)batch_cap, fit));
+        }
+    }
+
     CU(h->scores.ensure((size_t)n_centres * MMD_N_SCORES * sizeof(double)));
     CU(h->flags.ensure((size_t)n_centres * sizeof(int)));
     CU(h->misc_flag.ensure(sizeof(int)));
@@ -765,7 +787,7 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     CU(cudaMemsetAsync(h->flags.p, 0, (size_t)n_centres * sizeof(int), h->stream));
     if (with_null) CU(h->null_out.ensure((size_t)n_centres * h->n_perm * 6 * sizeof(double)));
 
-    // Clusters for the whole call, then plans for ranges of clusters ("chunks" of ~6 batches): the plan of chunk
+    // Clusters for the whole call, then plans for ranges of clusters ("chunks" of two or more batches): the plan of chunk
     // i+1 is built by host threads while the GPU executes chunk i.
     auto t_host0 = std::chrono::steady_clock::now();
     Clustering cl;
@@ -773,12 +795,14 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     const int n_clusters = (int)cl.cl_off.size() - 1;
     h->n_clusters += n_clusters;
     std::vector<int> chunk_start(1, 0);
+    const int chunk_target = std::max(2 * batch_cap, 12288);      // centres per chunk: whole batches, never more
     for (int c = 0, acc = 0; c < n_clusters; ++c) {
-        acc += cl.cl_off[c + 1] - cl.cl_off[c];
-        if (acc >= 6 * h->batch_centres && c + 1 < n_clusters) {
-            chunk_start.push_back(c + 1);
+        const int m = cl.cl_off[c + 1] - cl.cl_off[c];
+        if (acc > 0 && acc + m > chunk_target) {
+            chunk_start.push_back(c);
             acc = 0;
         }
+        acc += m;
     }
     chunk_start.push_back(n_clusters);
     const int n_chunks = (int)chunk_start.size() - 1;
@@ -793,7 +817,7 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
         pending.get();                                     // exposed host time: only what the GPU did not hide
         h->plan_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_host0).count();
         if (i + 1 < n_chunks) pending = std::async(std::launch::async, plan_chunk, i + 1);
-        rc = run_chunk(h, rows, plans[i & 1], total, k_max, kp, alpha, with_null, raw_yhat);
+        rc = run_chunk(h, rows, plans[i & 1], total, k_max, kp, alpha, with_null, raw_yhat, batch_cap);
         t_host0 = std::chrono::steady_clock::now();
     }
     if (pending.valid()) pending.wait();                   // an error path must not leave the planner running

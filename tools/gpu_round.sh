@@ -7,7 +7,7 @@ timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1
 timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2>&1
 timeout 900 python bench.py > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/bench.log
-SMALL="--centres-per-step 4096 --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
+SMALL="--centres-per-step 12288 --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
 KREG='regex:(factor_solve|predict_kernel|score_kernel|gemm_nt|prep_tasks|pack_transpose|knn_kernel|radius_kernel|half_to_double|row_sqnorm|gather_rows)'
 timeout 600 python bench.py $SMALL > gpurun_out/bench_small.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" -c 400 --csv \
