@@ -668,8 +668,8 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
         }
     }
 
-    // batches: whole clusters, at most batch_cap centres (a cluster may overshoot), the chunk split evenly so that no
-    // small remainder batch runs with the GPU half empty
+    // batches: whole clusters, about batch_cap centres each (a batch may overshoot by a cluster or two; the cap keeps
+    // half of the device memory free), the chunk split evenly so that no small remainder batch runs on an empty GPU
     const int chunk_tasks = plan.cl_off[n_clusters];
     const int n_batches = std::max(1, (chunk_tasks + batch_cap - 1) / batch_cap);
     const int batch_target = (chunk_tasks + n_batches - 1) / n_batches;
@@ -682,7 +682,8 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
         for (int g = plan.cl_grp_off[c]; g < plan.cl_grp_off[c + 1]; ++g) n_core_c += plan.grp_sp[g] > 0;
         const size_t u = (size_t)(plan.un_off[c + 1] - plan.un_off[c]);
         const size_t g = u * round_up((int)u, 8);
-        if (cur_tasks > 0 && (cur_tasks + m > batch_cap || cur_tasks + m / 2 > batch_target)) {
+        // close a batch at the cluster boundary nearest to the even split; the last batch takes whatever is left
+        if (cur_tasks > 0 && (int)batch_start.size() < n_batches && cur_tasks + m / 2 > batch_target) {
             batch_start.push_back(c);
             cur_tasks = 0;
             cur_pool = 0;
