@@ -34,9 +34,13 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo_bytes,
 }
 
 // A planes: (S x K x M) int8, M contiguous.  B planes: (S x N x K) int8, K contiguous.  out: (M x N) float64.
+// repeats > 1 (timing): the whole tile -- 84 MMAs, two barrier phases, the float64 epilogue when EPILOGUE -- is redone
+// from the resident planes; every CTA writes its own copy of the tile.
+template <bool EPILOGUE>
 __global__ void __launch_bounds__(128, 1) sliced_tile_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ B,
                                                              const double* __restrict__ scaleA, const double* __restrict__ scaleB,
-                                                             double* __restrict__ out, int* __restrict__ status) {
+                                                             double* __restrict__ out_all, int repeats, int* __restrict__ status) {
+    double* out = out_all + (size_t)blockIdx.x * M * N;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* As = smem;                       // plane t at As + t * A_PLANE, MN-major canonical layout
     uint8_t* Bs = smem + S * A_PLANE;         // plane u at Bs + u * B_PLANE, K-major canonical layout
@@ -74,7 +78,8 @@ __global__ void __launch_bounds__(128, 1) sliced_tile_kernel(const int8_t* __res
     bool ok = true;
 
     // two passes over the weights, smallest terms first: w = 5, 4, 3 and then w = 2, 1, 0
-    for (int pass = 0; pass < 2 && ok; ++pass) {
+    for (int it = 0; it < 2 * repeats && ok; ++it) {
+        const int pass = it & 1;
         const int w_hi = pass == 0 ? S - 1 : S - 4;          // 5 | 2
         if (tid == 0) {
             const uint32_t a0 = smem_u32(As), b0 = smem_u32(Bs);
@@ -110,14 +115,14 @@ __global__ void __launch_bounds__(128, 1) sliced_tile_kernel(const int8_t* __res
                 ".reg .pred p;\n\t"
                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
                 "selp.u32 %0, 1, 0, p;\n\t"
-                "}\n" : "=r"(done) : "r"(smem_u32(&bar)), "r"((uint32_t)(pass & 1)) : "memory");
+                "}\n" : "=r"(done) : "r"(smem_u32(&bar)), "r"((uint32_t)(it & 1)) : "memory");
         }
         if (!done) {
             if (lane == 0) atomicExch(status, 2 + pass);
             ok = false;
         }
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        if (ok) {
+        if (ok && EPILOGUE) {
             const double sa = scaleA[row];
             for (int c0 = 0; c0 < N; c0 += 16) {
                 double acc[16];
@@ -194,7 +199,7 @@ int main() {
     CK(cudaMalloc(&dB, hB.size()));
     CK(cudaMalloc(&dsA, sizeof(double) * M));
     CK(cudaMalloc(&dsB, sizeof(double) * N));
-    CK(cudaMalloc(&dout, sizeof(double) * M * N));
+    CK(cudaMalloc(&dout, sizeof(double) * M * N * p.multiProcessorCount));
     CK(cudaMalloc(&dstatus, sizeof(int)));
     CK(cudaMemcpy(dA, hA.data(), hA.size(), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(dB, hB.data(), hB.size(), cudaMemcpyHostToDevice));
@@ -203,8 +208,9 @@ int main() {
     CK(cudaMemset(dout, 0xff, sizeof(double) * M * N));
     CK(cudaMemset(dstatus, 0, sizeof(int)));
     const int smem_bytes = S * (A_PLANE + B_PLANE);
-    CK(cudaFuncSetAttribute(sliced_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    sliced_tile_kernel<<<1, 128, smem_bytes>>>(dA, dB, dsA, dsB, dout, dstatus);
+    CK(cudaFuncSetAttribute(sliced_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    CK(cudaFuncSetAttribute(sliced_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    sliced_tile_kernel<true><<<1, 128, smem_bytes>>>(dA, dB, dsA, dsB, dout, 1, dstatus);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     int status = 0;
@@ -242,5 +248,33 @@ int main() {
     printf("{\"gpu\": \"%s\", \"tile\": \"%dx%dx%d float64 via %d int8 digits, %d slice-pair GEMMs\", \"status\": %d, "
            "\"bit_mismatches_vs_host_integer_arithmetic\": %ld, \"max_error_vs_float64_product_rel_to_max\": %.3e}\n",
            p.name, M, N, K, S, S * (S + 1) / 2, status, bit_mismatches, max_rel);
+    if (status == 0 && bit_mismatches == 0) {
+        // one CTA per SM, the tile redone `reps` times: time per tile with and without the float64 epilogue
+        const int reps = 400, sms = p.multiProcessorCount;
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        float ms_epi = 1e30f, ms_mma = 1e30f;
+        for (int r = 0; r < 4; ++r) {
+            float ms;
+            cudaEventRecord(e0);
+            sliced_tile_kernel<true><<<sms, 128, smem_bytes>>>(dA, dB, dsA, dsB, dout, reps, dstatus);
+            cudaEventRecord(e1);
+            CK(cudaEventSynchronize(e1));
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (r > 0 && ms < ms_epi) ms_epi = ms;
+            cudaEventRecord(e0);
+            sliced_tile_kernel<false><<<sms, 128, smem_bytes>>>(dA, dB, dsA, dsB, dout, reps, dstatus);
+            cudaEventRecord(e1);
+            CK(cudaEventSynchronize(e1));
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (r > 0 && ms < ms_mma) ms_mma = ms;
+        }
+        CK(cudaMemcpy(&status, dstatus, sizeof(int), cudaMemcpyDeviceToHost));
+        const double ops = 2.0 * M * N * K * (S * (S + 1) / 2);
+        printf("{\"timed_status\": %d, \"us_per_tile_mma_only\": %.3f, \"us_per_tile_with_float64_epilogue\": %.3f, "
+               "\"mma_only_tops\": %.1f, \"note\": \"per SM; the production tile has K = 768, i.e. 6x the MMAs per epilogue\"}\n",
+               status, ms_mma * 1e3 / reps, ms_epi * 1e3 / reps, ops * reps * sms / ms_mma * 1e-9);
+    }
     return 0;
 }
