@@ -32,6 +32,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "searchlight centers/sec (750-nbr ridge+pairwise acc)"
+WORKLOAD = ("searchlight imagebind --n-neighbors 750 modality-agnostic, one synthetic fsaverage7-sized hemisphere "
+            "(BASELINE.json configs[1])")
 UNIT = "centers/s"
 
 
@@ -427,8 +429,7 @@ def run_ours(args):
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(dev_s / K * 1e3, 3), "higher_is_better": True,
             "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "searchlight imagebind --n-neighbors 750 modality-agnostic, one synthetic "
-                                   "fsaverage7-sized hemisphere (BASELINE.json configs[1])",
+            "config": {"workload": WORKLOAD,
                        "n_vertices": V, "n_neighbors": k, "n_train": args.n_train, "n_test": 140, "n_imagery": 3,
                        "n_dims": args.n_dims, "alpha": 1.0, "centres_per_step_per_gpu": cps,
                        "sharding": (f"{world} hemisphere job(s), one per GPU, score maps all-gathered" if weak else
@@ -495,8 +496,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 2),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "searchlight imagebind --n-neighbors 750 modality-agnostic (BASELINE.json configs[1]), "
-                               "bounded sample of centres", "n_neighbors": k, "n_train": n_tr, "n_dims": D},
+        # the own arm's workload; each step is a bounded sample of its centres (cpu_baseline.sample)
+        "config": {"workload": WORKLOAD, "n_vertices": int(len(mesh.coords)), "n_neighbors": k, "n_train": n_tr,
+                   "n_test": 140, "n_imagery": 3, "n_dims": D, "alpha": 1.0, "centres_per_step": n_c},
         "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "CPU restatement of the reference loop (the reference is Python + sklearn/scipy and cannot travel "
