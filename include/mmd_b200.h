@@ -30,8 +30,8 @@ typedef struct mmd_handle mmd_handle;
 #define MMD_N_SCORES 8          /* order: see MMD_SCORE_NAMES in mmd_score_name() */
 #define MMD_EVAL_PAD 144        /* test + imagery trials per centre must be <= 143 */
 
-/* Number of stage timers reported by mmd_get_stats (pack, xty, prep, syrk, factor_solve, predict, score, knn, null). */
-#define MMD_N_STAGES 9
+/* Number of stage timers reported by mmd_get_stats (pack, xty, prep, syrk, factor_solve, predict, score, knn, null, reroute). */
+#define MMD_N_STAGES 10
 
 int mmd_create(int device, mmd_handle** out);
 void mmd_destroy(mmd_handle* h);
@@ -172,14 +172,31 @@ const char* mmd_stage_name(int i);
 /* More counters since the last mmd_reset_stats: [0] batches (every batch launches each per-centre kernel once),
  * [1] shared-core factorisations, [2] centres that used a shared core, [3] sum of their shared prefix lengths,
  * [4] host microseconds spent grouping centres (clusters, unions, shared cores), [5] host microseconds to hand the
- * adjacency to the device;
+ * adjacency to the device, [6] centres whose predictions were redone by the float64 kernels because a comparison sat
+ * inside the error bound of the integer prediction GEMM (mmd_set_predict_mode);
  * solve_flops = float64 flops executed by the factorisation / triangular-solve stage. */
-#define MMD_N_COUNTERS 6
+#define MMD_N_COUNTERS 7
 int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* solve_flops);
 
 /* Prefix sharing: up to `group_size` neighbouring centres factor the part of their normal matrices that belongs to
  * the neighbours they all share only once (1 = off; default 8).  The scores do not depend on it. */
 int mmd_set_group_size(mmd_handle* h, int group_size);
+
+/* How estimator.predict (searchlight.py:58-59) is executed.
+ *   1 (default)  tcgen05 tensor cores: both float64 operands are cut into six signed 7-bit digits, the digit-pair
+ *                products run as kind::i8 GEMMs with exact int32 accumulation in tensor memory and are recombined in
+ *                float64; the scoring kernel bounds the effect of the dropped digits on every comparison and hands the
+ *                centres it cannot vouch for to the float64 kernels (counter [6] above), so the scores are the ones
+ *                float64 arithmetic gives;
+ *   0            float64 tensor pipe (DMMA) for every centre.
+ * The environment variable MMD_B200_PREDICT=f64 selects 0 at mmd_create. */
+int mmd_set_predict_mode(mmd_handle* h, int mode);
+
+/* Diagnostics: after the next mmd_searchlight* call mmd_get_margins returns, per centre, the smallest absolute
+ * difference between a prediction's distance to its own candidate and to any other candidate it is compared with
+ * (eval.py:107-113) -- how far the centre is from a flipped comparison.  margins_out: (n_centres) float64 HOST. */
+int mmd_enable_margins(mmd_handle* h, int on);
+int mmd_get_margins(mmd_handle* h, double* margins_out, int n_centres);
 
 /* Tuning knobs (0 keeps the default): centres per cluster, max centres per batch. */
 int mmd_configure(mmd_handle* h, int cluster_size, int batch_centres, int host_threads);

@@ -7,7 +7,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MMD_B200_LIB") or os.path.join(_HERE, "libmmd_b200.so")
 
 N_SCORES = 8
-N_STAGES = 9
+N_STAGES = 10
+N_COUNTERS = 7
 N_NULL_SCORES = 6
 EVAL_PAD = 144
 
@@ -16,6 +17,7 @@ EXPORTS = [
     "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
     "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels", "mmd_check_guards", "mmd_guard_selftest",
+    "mmd_set_predict_mode", "mmd_enable_margins", "mmd_get_margins",
 ]
 
 _lib = None
@@ -81,6 +83,12 @@ def load():
     lib.mmd_get_stats.restype = i32
     lib.mmd_get_counters.argtypes = [vp, C.POINTER(i64), C.POINTER(dbl)]
     lib.mmd_get_counters.restype = i32
+    lib.mmd_set_predict_mode.argtypes = [vp, i32]
+    lib.mmd_set_predict_mode.restype = i32
+    lib.mmd_enable_margins.argtypes = [vp, i32]
+    lib.mmd_enable_margins.restype = i32
+    lib.mmd_get_margins.argtypes = [vp, vp, i32]
+    lib.mmd_get_margins.restype = i32
     lib.mmd_set_group_size.argtypes = [vp, i32]
     lib.mmd_set_group_size.restype = i32
     lib.mmd_reset_stats.argtypes = [vp]

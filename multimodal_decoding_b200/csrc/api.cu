@@ -25,8 +25,8 @@ using namespace mmd;
 
 namespace {
 
-enum Stage { ST_PACK = 0, ST_XTY, ST_PREP, ST_SYRK, ST_SOLVE, ST_PREDICT, ST_SCORE, ST_KNN, ST_NULL };
-const char* kStageNames[MMD_N_STAGES] = {"pack", "xty", "prep", "syrk", "factor_solve", "predict", "score", "knn", "null"};
+enum Stage { ST_PACK = 0, ST_XTY, ST_PREP, ST_SYRK, ST_SOLVE, ST_PREDICT, ST_SCORE, ST_KNN, ST_NULL, ST_REROUTE };
+const char* kStageNames[MMD_N_STAGES] = {"pack", "xty", "prep", "syrk", "factor_solve", "predict", "score", "knn", "null", "reroute"};
 const char* kScoreNames[MMD_N_SCORES] = {
     "pairwise_acc_captions",
     "pairwise_acc_images",
@@ -146,6 +146,14 @@ struct mmd_handle {
     PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
     DevBuf st_in, st_edges, st_label, st_count, st_out;     // group-level statistics
     DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
+    // integer prediction GEMM (predict_i8.cu): digit planes of XtY (per upload) and of every centre's Zt (per batch),
+    // their scales, the score kernel's tolerance input, the list of centres handed back to the float64 kernels
+    DevBuf xplanes, sX, colmax, zplanes, sZ, amp2, i8_status, reroute_list, reroute_counts, margins;
+    int predict_mode = 1;           // 1: tcgen05 int8 digit GEMM + float64 reroute of guarded centres; 0: float64 DMMA kernel
+    int n_sms = 148;
+    int call_batches = 0;           // batches of the current searchlight call (index into reroute_counts)
+    bool want_margins = false;
+    int64_t n_rerouted = 0;
     int n_perm = 0;
     std::vector<int> int_of_test;   // position in test_ids order -> internal evaluation row (captions first)
     // knobs
@@ -446,6 +454,9 @@ void build_plan(const Rows& rows, int V, const Clustering& cl, int c_begin, int 
     }
 }
 
+constexpr int MAX_CALL_BATCHES = 4096;
+constexpr double I8_EPS_UNIT = 7.2 / 4398046511104.0;      // 7.2 * 2^-42, see score.cu
+
 int run_xty(mmd_handle* h) {
     GemmProblem p{};
     p.A = h->Xt.as<__half>();
@@ -464,6 +475,16 @@ int run_xty(mmd_handle* h) {
     span_begin(h, ST_XTY);
     CU(launch_gemm_gather(h->probs.as<GemmProblem>(), 1, p.M, p.N, h->stream));
     span_end(h);
+    if (h->predict_mode == 1) {
+        // digit planes of the cross-covariance for the integer prediction GEMM (once per upload)
+        CU(h->xplanes.ensure((size_t)I8_DIGITS * h->V * h->Dp));
+        CU(h->sX.ensure((size_t)h->Dp * sizeof(double)));
+        CU(h->colmax.ensure((size_t)h->Dp * sizeof(unsigned long long)));
+        span_begin(h, ST_XTY);
+        CU(launch_slice_xty(h->XtY.as<double>(), h->V, h->Dp, h->xplanes.as<int8_t>(), h->sX.as<double>(),
+                            h->colmax.as<unsigned long long>(), h->stream));
+        span_end(h, 3);
+    }
     return 0;
 }
 
@@ -612,9 +633,8 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     pp.n_img = h->n_img;
     pp.n_im = h->n_im;
     pp.standardize = raw_yhat ? 0 : 1;
-    span_begin(h, ST_PREDICT);
-    CU(launch_predict(pp, h->stream));
-    span_end(h);
+    pp.task_list = nullptr;
+    pp.n_list = nullptr;
 
     ScoreParams sc{};
     sc.tasks = sp.tasks;
@@ -628,9 +648,63 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     sc.n_im = h->n_im;
     sc.scores = h->scores.as<double>();
     sc.dist_out = with_null ? h->dist.as<double>() : nullptr;
-    span_begin(h, ST_SCORE);
-    CU(launch_score(sc, h->stream));
-    span_end(h);
+    sc.margin_out = h->want_margins ? h->margins.as<double>() : nullptr;
+
+    const bool i8 = h->predict_mode == 1 && !raw_yhat;
+    if (!i8) {
+        span_begin(h, ST_PREDICT);
+        CU(launch_predict(pp, h->stream));
+        span_end(h);
+        span_begin(h, ST_SCORE);
+        CU(launch_score(sc, h->stream));
+        span_end(h);
+    } else {
+        // integer GEMM on the tcgen05 tensor cores; the score kernel lists the centres whose comparisons are too close to
+        // the GEMM's error bound, and those are redone by the float64 kernels (device-side list, no host round trip)
+        if (h->call_batches >= MAX_CALL_BATCHES) return fail(h, "internal: more than %d batches in one call", MAX_CALL_BATCHES);
+        int* count = h->reroute_counts.as<int>() + h->call_batches++;
+        PredictI8Params ip{};
+        ip.tasks = sp.tasks;
+        ip.n_tasks = n_tasks;
+        ip.kp_max = kp;
+        ip.V = h->V;
+        ip.Dp = h->Dp;
+        ip.sX = h->sX.as<double>();
+        ip.sZ = h->sZ.as<double>();
+        ip.yhat = h->yhat.as<double>();
+        ip.amp2 = h->amp2.as<double>();
+        ip.n_cap = h->n_cap;
+        ip.n_img = h->n_img;
+        ip.n_im = h->n_im;
+        ip.standardize = 1;
+        ip.status = h->i8_status.as<int>();
+        span_begin(h, ST_PREDICT);
+        CU(cudaMemsetAsync(h->amp2.p, 0, (size_t)n_tasks * 4 * sizeof(double), h->stream));
+        CU(launch_slice_zt(sp.tasks, n_tasks, kp, h->work.as<double>(), h->zplanes.as<int8_t>(), h->sZ.as<double>(), h->stream));
+        CU(launch_predict_i8(ip, h->xplanes.as<int8_t>(), h->zplanes.as<int8_t>(), h->n_sms, h->stream));
+        span_end(h, 2);
+        sc.amp2 = h->amp2.as<double>();
+        sc.sZ = h->sZ.as<double>();
+        sc.eps_unit = I8_EPS_UNIT;
+        sc.reroute_list = h->reroute_list.as<int>();
+        sc.reroute_count = count;
+        span_begin(h, ST_SCORE);
+        CU(launch_score(sc, h->stream));
+        span_end(h);
+        // second pass, float64, over the listed centres only (CTAs beyond the count leave at once)
+        pp.task_list = h->reroute_list.as<int>();
+        pp.n_list = count;
+        sc.task_list = pp.task_list;
+        sc.n_list = count;
+        sc.amp2 = nullptr;
+        sc.sZ = nullptr;
+        sc.reroute_list = nullptr;
+        sc.reroute_count = nullptr;
+        span_begin(h, ST_REROUTE);
+        CU(launch_predict(pp, h->stream));
+        CU(launch_score(sc, h->stream));
+        span_end(h, 2);
+    }
     if (with_null) {
         NullParams np{};
         np.tasks = sp.tasks;
@@ -707,6 +781,12 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
     CU(h->core_work.ensure(std::max<size_t>((size_t)max_core * (sp_max + EVAL_PAD) * sp_max, 1) * sizeof(double)));
     CU(h->group_flags.ensure(std::max<size_t>(max_core, 1) * sizeof(int)));
     if (with_null) CU(h->dist.ensure((size_t)max_tasks * NULL_DIST_ROWS * EVAL_PAD * sizeof(double)));
+    if (h->predict_mode == 1 && !raw_yhat) {
+        CU(h->zplanes.ensure((size_t)max_tasks * I8_DIGITS * EVAL_PAD * kp));
+        CU(h->sZ.ensure((size_t)max_tasks * EVAL_PAD * sizeof(double)));
+        CU(h->amp2.ensure((size_t)max_tasks * 4 * sizeof(double)));
+        CU(h->reroute_list.ensure((size_t)max_tasks * sizeof(int)));
+    }
 
     for (size_t b = 0; b + 1 < batch_start.size(); ++b)
         if (run_batch(h, rows, plan, batch_start[b], batch_start[b + 1], k_max, kp, sp_max, alpha, with_null, raw_yhat)) return 1;
@@ -771,11 +851,12 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
         size_t free_b = 0, total_b = 0;
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
             const size_t held = h->work.bytes + h->yhat.bytes + h->core_work.bytes + h->nbr_sorted.bytes + h->loc.bytes +
-                                h->dist.bytes + h->gram_pool.bytes;
+                                h->dist.bytes + h->gram_pool.bytes + h->zplanes.bytes;
             const double per_centre = 1.25 * (double)(kp + EVAL_PAD) * kp * sizeof(double) +
                                       (double)YHAT_ROWS * h->Dp * sizeof(double) + 2.5 * kp * sizeof(int) +
                                       0.1 * (double)kp * kp * sizeof(double) +
-                                      (with_null ? (double)NULL_DIST_ROWS * EVAL_PAD * sizeof(double) : 0.0);
+                                      (with_null ? (double)NULL_DIST_ROWS * EVAL_PAD * sizeof(double) : 0.0) +
+                                      (h->predict_mode == 1 ? (double)I8_DIGITS * EVAL_PAD * kp : 0.0);
             const double fit = 0.5 * ((double)free_b + (double)held) / per_centre;
             batch_cap = (int)std::max(256.0, std::min((double)batch_cap, fit));
         }
@@ -787,6 +868,14 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     CU(cudaMemsetAsync(h->misc_flag.p, 0, sizeof(int), h->stream));
     CU(cudaMemsetAsync(h->flags.p, 0, (size_t)n_centres * sizeof(int), h->stream));
     if (with_null) CU(h->null_out.ensure((size_t)n_centres * h->n_perm * 6 * sizeof(double)));
+    h->call_batches = 0;
+    if (h->predict_mode == 1 && !raw_yhat) {
+        CU(h->reroute_counts.ensure((size_t)MAX_CALL_BATCHES * sizeof(int)));
+        CU(h->i8_status.ensure(sizeof(int)));
+        CU(cudaMemsetAsync(h->reroute_counts.p, 0, (size_t)MAX_CALL_BATCHES * sizeof(int), h->stream));
+        CU(cudaMemsetAsync(h->i8_status.p, 0, sizeof(int), h->stream));
+    }
+    if (h->want_margins) CU(h->margins.ensure((size_t)n_centres * sizeof(double)));
 
     // Clusters for the whole call, then plans for ranges of clusters ("chunks" of two or more batches): the plan of chunk
     // i+1 is built by host threads while the GPU executes chunk i.
@@ -841,7 +930,9 @@ std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
                       &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
                       &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
-                      &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval};
+                      &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval,
+                      &h->xplanes, &h->sX, &h->colmax, &h->zplanes, &h->sZ, &h->amp2, &h->i8_status, &h->reroute_list,
+                      &h->reroute_counts, &h->margins};
 }
 
 // the stream must have passed mmd_upload's kernels (any later synchronisation of h->stream will do)
@@ -850,6 +941,19 @@ void release_upload_staging(mmd_handle* h) {
     h->up_y.release();
     h->up_train.release();
     h->up_eval.release();
+}
+
+// after the stream is synchronised: how many centres went back to the float64 kernels; protocol errors of the integer GEMM
+int collect_i8_stats(mmd_handle* h) {
+    if (h->call_batches == 0) return 0;
+    std::vector<int> counts(h->call_batches);
+    int status = 0;
+    CU(cudaMemcpy(counts.data(), h->reroute_counts.p, counts.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(&status, h->i8_status.p, sizeof(int), cudaMemcpyDeviceToHost));
+    for (int c : counts) h->n_rerouted += c;
+    h->call_batches = 0;
+    if (status) return fail(h, "predict_i8_kernel: a bounded wait ran out (role %d); results are not valid", status);
+    return 0;
 }
 
 int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double* scores_out, int32_t* flags_out,
@@ -871,6 +975,7 @@ int searchlight_and_fetch(mmd_handle* h, const Rows& rows, double alpha, double*
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
     release_upload_staging(h);
+    if (collect_i8_stats(h)) return 1;
     return report_input_flags(h, bad, y_bad, who);
 }
 
@@ -897,6 +1002,8 @@ int mmd_create(int device, mmd_handle** out) {
         delete h;
         return 4;
     }
+    cudaDeviceGetAttribute(&h->n_sms, cudaDevAttrMultiProcessorCount, device);
+    if (const char* e = getenv("MMD_B200_PREDICT")) h->predict_mode = strcmp(e, "f64") == 0 ? 0 : 1;
     *out = h;
     return 0;
 }
@@ -970,7 +1077,7 @@ void mmd_reset_stats(mmd_handle* h) {
     h->n_clusters = 0;
     h->syrk_flops = 0.0;
     h->solve_flops = 0.0;
-    h->n_batches = h->n_core_tasks = h->n_grouped = h->sum_sp = h->plan_us = h->adj_h2d_us = 0;
+    h->n_batches = h->n_core_tasks = h->n_grouped = h->sum_sp = h->plan_us = h->adj_h2d_us = h->n_rerouted = 0;
 }
 
 int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* solve_flops) {
@@ -982,8 +1089,34 @@ int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* so
         counters[3] = h->sum_sp;
         counters[4] = h->plan_us;
         counters[5] = h->adj_h2d_us;
+        counters[6] = h->n_rerouted;
     }
     if (solve_flops) *solve_flops = h->solve_flops;
+    return 0;
+}
+
+int mmd_set_predict_mode(mmd_handle* h, int mode) {
+    if (!h) return 1;
+    if (mode != 0 && mode != 1) return fail(h, "mmd_set_predict_mode: mode must be 0 (float64) or 1 (tcgen05 int8 digits)");
+    if (mode == 1 && h->uploaded && !h->xplanes.p)
+        return fail(h, "mmd_set_predict_mode: switch to the integer GEMM before mmd_upload (its digit planes are cut there)");
+    h->predict_mode = mode;
+    return 0;
+}
+
+int mmd_enable_margins(mmd_handle* h, int on) {
+    if (!h) return 1;
+    h->want_margins = on != 0;
+    return 0;
+}
+
+int mmd_get_margins(mmd_handle* h, double* margins_out, int n_centres) {
+    if (!h) return 1;
+    if (!margins_out || n_centres < 0) return fail(h, "mmd_get_margins: bad arguments");
+    if ((size_t)n_centres * sizeof(double) > h->margins.bytes) return fail(h, "mmd_get_margins: no margins recorded for %d centres", n_centres);
+    CU(cudaSetDevice(h->device));
+    CU(cudaMemcpyAsync(margins_out, h->margins.p, (size_t)n_centres * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
     return 0;
 }
 
@@ -1130,7 +1263,7 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
     h->n_test = n_test;
     h->n_im = n_imagery;
     h->D = n_dims;
-    h->Dp = round_up(n_dims, 64);
+    h->Dp = round_up(n_dims, 128);         // 128-feature tiles of the integer prediction GEMM
     // evaluation rows in the internal order: captions, images, imagery
     std::vector<int> eval_ids;
     h->n_cap = 0;
@@ -1317,6 +1450,8 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
     if (flags_out) CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
+    release_upload_staging(h);
+    if (collect_i8_stats(h)) return 1;
     return report_input_flags(h, bad, y_bad, "mmd_searchlight_null");
 }
 

@@ -617,14 +617,11 @@ size_t factor_solve_smem_bytes() { return (size_t)(PIPE_DOUBLES + NB * LDD) * si
 
 cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s) {
     const size_t smem = factor_solve_smem_bytes();
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(factor_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(factor_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    // function attributes are per device: set on every launch (several engines on different GPUs may share the process)
+    cudaError_t e = cudaFuncSetAttribute(factor_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(factor_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (e != cudaSuccess) return e;
     if (p.kp_max % NB != 0) return cudaErrorInvalidValue;
     factor_solve_kernel<<<p.n_tasks, THREADS, smem, s>>>(p);
     return cudaGetLastError();

@@ -114,13 +114,10 @@ __global__ void __launch_bounds__(256, 2) gemm_nt_f16_f64_kernel(const GemmProbl
 }
 
 cudaError_t launch_gemm_gather(const GemmProblem* probs_dev, int n_problems, int max_m, int max_n, cudaStream_t s) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_nt_f16_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)gemm_gather_smem_bytes());
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    // function attributes are per device: set on every launch (several engines on different GPUs may share the process)
+    cudaError_t e = cudaFuncSetAttribute(gemm_nt_f16_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)gemm_gather_smem_bytes());
+    if (e != cudaSuccess) return e;
     dim3 grid((max_n + BN - 1) / BN, (max_m + BM - 1) / BM, n_problems);
     gemm_nt_f16_f64_kernel<<<grid, 256, gemm_gather_smem_bytes(), s>>>(probs_dev);
     return cudaGetLastError();

@@ -73,6 +73,9 @@ struct PredictParams {
     double* yhat;         // per task: YHAT_ROWS x Dp (layout below)
     int n_cap, n_img, n_im;
     int standardize;      // 1: rows are z-scored per prediction group (the scoring input); 0: raw predictions
+    // optional indirection: blockIdx.y = b works on task task_list[b] if b < *n_list and leaves otherwise
+    const int* task_list;
+    const int* n_list;
 };
 // Rows of a task's yhat block, written by predict and read by score:
 //   0 .. n_eval-1            predictions of [caption test | image test | imagery] trials; with `standardize` each
@@ -85,6 +88,36 @@ constexpr int YHAT_ROWS = 152;
 size_t predict_smem_bytes();
 cudaError_t launch_predict(const PredictParams& p, cudaStream_t s);
 
+// ---- predict_i8.cu -----------------------------------------------------------------------
+// The same product on tcgen05 tensor cores: both operands cut into I8_DIGITS signed 7-bit digits behind power-of-two
+// scales, digit-pair GEMMs (kind::i8, int32 accumulators in tensor memory), float64 recombination (see the file header).
+constexpr int I8_DIGITS = 6;
+struct PredictI8Params {
+    const CentreTask* tasks;
+    int n_tasks;
+    int kp_max;           // row pitch of the Zt digit planes (bytes) = largest task.kp of the launch, a multiple of 64
+    int V;                // rows per XtY digit plane
+    int Dp;               // feature count rounded up to 128
+    const double* sX;     // (Dp) power-of-two scale of every XtY column
+    const double* sZ;     // (n_tasks x EVAL_PAD) power-of-two scale of every Zt row
+    double* yhat;         // as PredictParams::yhat
+    double* amp2;         // (n_tasks x 4), zeroed by the caller: sum over the features of (sX / sd_g)^2 for the three
+                          // prediction groups and of sX^2 -- the score kernel's tolerance input
+    int n_cap, n_img, n_im;
+    int standardize;
+    int* status;          // set non-zero when a bounded wait ran out (protocol error; 0 in every correct run)
+};
+size_t predict_i8_smem_bytes();
+// planes: (I8_DIGITS x V x Dp) int8, sX: (Dp), colmax_ws: (Dp) scratch
+cudaError_t launch_slice_xty(const double* XtY, int V, int Dp, int8_t* planes, double* sX, unsigned long long* colmax_ws,
+                             cudaStream_t s);
+// zplanes: (n_tasks x I8_DIGITS x EVAL_PAD x kp_max) int8, sZ: (n_tasks x EVAL_PAD); Zt is read from `work` as in PredictParams
+cudaError_t launch_slice_zt(const CentreTask* tasks, int n_tasks, int kp_max, const double* work, int8_t* zplanes, double* sZ,
+                            cudaStream_t s);
+cudaError_t launch_predict_i8(const PredictI8Params& p, const int8_t* xplanes, const int8_t* zplanes, int n_sms, cudaStream_t s);
+cudaError_t make_tensor_map_u8(void* out_map, const void* base, uint64_t cols, uint64_t rows, uint64_t pitch, uint32_t box_cols,
+                               uint32_t box_rows, int swizzle_bytes);
+
 // ---- score.cu ----------------------------------------------------------------------------
 struct ScoreParams {
     const CentreTask* tasks;
@@ -96,6 +129,16 @@ struct ScoreParams {
     int n_cap, n_img, n_im;
     double* scores;            // (n_centres x 8), written at row task.centre
     double* dist_out;          // optional: per task NULL_DIST_ROWS x EVAL_PAD cosine distances (null-distribution input)
+    // optional indirection: CTA b works on task task_list[b] if b < *n_list and leaves otherwise (device pointers)
+    const int* task_list;
+    const int* n_list;
+    // optional guard for predictions that came from predict_i8.cu (all nullptr / 0 for float64 predictions):
+    const double* amp2;        // PredictI8Params::amp2
+    const double* sZ;          // PredictI8Params::sZ
+    double eps_unit;           // per-term truncation bound of the integer GEMM in scale units (7.2 * 2^-42)
+    int* reroute_list;         // tasks with a comparison inside its tolerance are appended here ...
+    int* reroute_count;        // ... at position atomicAdd(reroute_count, 1)
+    double* margin_out;        // optional (n_centres): smallest |d_own - d_other| over the counted comparisons
 };
 // rows 0..n_eval-1: standardised predictions (captions, images, imagery); rows EVAL_PAD..: raw imagery predictions
 constexpr int NULL_DIST_ROWS = 160;

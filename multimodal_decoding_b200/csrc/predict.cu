@@ -29,7 +29,11 @@ __global__ void __launch_bounds__(THREADS, 2) predict_kernel(PredictParams prm) 
     double* Bs = As + STAGES * A_STAGE;
     int* nbr_sm = reinterpret_cast<int*>(Bs + STAGES * B_STAGE);
 
-    const int task_id = blockIdx.y;
+    int task_id = blockIdx.y;
+    if (prm.task_list) {
+        if (task_id >= *prm.n_list) return;
+        task_id = prm.task_list[task_id];
+    }
     const CentreTask task = prm.tasks[task_id];
     const int k = task.k, kp = task.kp, Dp = prm.Dp;
     const int d0 = blockIdx.x * BN;
@@ -151,13 +155,10 @@ __global__ void __launch_bounds__(THREADS, 2) predict_kernel(PredictParams prm) 
 }
 
 cudaError_t launch_predict(const PredictParams& p, cudaStream_t s) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(predict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)predict_smem_bytes());
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    // function attributes are per device: set on every launch (several engines on different GPUs may share the process)
+    cudaError_t e = cudaFuncSetAttribute(predict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)predict_smem_bytes());
+    if (e != cudaSuccess) return e;
+    if (p.n_tasks <= 0) return cudaSuccess;
     if (p.kp_max > 2048 || p.n_im > YHAT_ROWS - EVAL_PAD) return cudaErrorInvalidValue;
     dim3 grid(p.Dp / BN, p.n_tasks);
     predict_kernel<<<grid, THREADS, predict_smem_bytes(), s>>>(p);

@@ -9,6 +9,15 @@
 // One CTA per centre.  The (152 x 144) x Dp inner products run on the fp64 tensor pipe in two passes of 80
 // rows; both operands are float64 in global memory and go through a 4-stage cp.async ring, so the loop has
 // the same shape as predict.cu's.  Row norms are accumulated from the staged tiles.
+//
+// Guard for the integer prediction GEMM (predict_i8.cu): that kernel's predictions carry a bounded truncation error
+//   |yhat_i8 - yhat| <= eps0 sX[d] sZ[e],   eps0 = 7.2 k 2^-42
+// (k terms, each short of the exact product by at most (5.03 + 2) 2^-42 scale units, plus the float64 recombination).
+// Propagated through the per-feature z-scoring (|z' - z| <= 2 (|z| + 2) eps0 sX sZmax_g / sd, |z| <= (n_g-1)/sqrt(n_g))
+// and the cosine distance (a row perturbed by eta moves the difference of two of its distances by at most
+// 4 |eta| / |row|) this gives every prediction row a tolerance; a centre with any counted comparison whose two
+// distances are closer than the row's tolerance is appended to `reroute_list` and redone by the float64 kernels.
+// Every other centre's comparisons are the ones exact arithmetic on the same operands would produce.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -39,8 +48,15 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
     double* dsame_sm = nrm_sm + 160;                             // [160]
     double* dcross_sm = dsame_sm + 160;                          // [160]
     __shared__ int cnt_sm[8];
+    __shared__ double tolc_sm[160];                              // guard: 4 |eta_row| (0 without the guard)
+    __shared__ int risky_sm;
+    __shared__ unsigned long long margin_sm;                     // bits of the smallest |d_own - d_other| over counted comparisons
 
-    const int task_id = blockIdx.x;
+    int task_id = blockIdx.x;
+    if (prm.task_list) {
+        if (task_id >= *prm.n_list) return;
+        task_id = prm.task_list[task_id];
+    }
     const CentreTask task = prm.tasks[task_id];
     const double* yhat = prm.yhat + (long)task_id * YHAT_ROWS * Dp;
     const int n_cap = prm.n_cap, n_img = prm.n_img, n_im = prm.n_im;
@@ -48,7 +64,31 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
     const int tid = threadIdx.x, lane = tid & 31, warp = (tid >> 5) % 9, wm = (tid >> 5) / 9;
 
     if (tid < 8) cnt_sm[tid] = 0;
-    for (int i = tid; i < 160; i += THREADS) nrm_sm[i] = 0.0;
+    if (tid == 0) {
+        risky_sm = 0;
+        margin_sm = 0x7ff0000000000000ull;
+    }
+    for (int i = tid; i < 160; i += THREADS) {
+        nrm_sm[i] = 0.0;
+        double tc = 0.0;
+        if (prm.amp2) {
+            const double eps0 = prm.eps_unit * (double)task.k;
+            const double* a2 = prm.amp2 + (long)task_id * 4;
+            const double* sz = prm.sZ + (long)task_id * EVAL_PAD;
+            const int g = i < n_eval ? (i >= n_cap) + (i >= n_test) : -1;
+            if (g >= 0) {
+                const int lo = g == 0 ? 0 : g == 1 ? n_cap : n_test, hi = g == 0 ? n_cap : g == 1 ? n_test : n_eval;
+                double szmax = 0.0;
+                for (int r = lo; r < hi; ++r) szmax = fmax(szmax, sz[r]);
+                const double n_g = (double)(hi - lo);
+                const double zmax = n_g > 1.0 ? (n_g - 1.0) / sqrt(n_g) : 0.0;
+                tc = 4.0 * 2.0 * (zmax + 2.0) * eps0 * szmax * sqrt(a2[g]);
+            } else if (i >= RAW_ROW0 && i < RAW_ROW0 + n_im) {
+                tc = 4.0 * eps0 * sz[n_test + (i - RAW_ROW0)] * sqrt(a2[3]);
+            }
+        }
+        tolc_sm[i] = tc;
+    }
     // rows of the second pass beyond YHAT_ROWS are never loaded: keep them finite
     for (int i = tid; i < STAGES * A_STAGE; i += THREADS) As[i] = 0.0;
     __syncthreads();
@@ -57,6 +97,8 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
     int cnt[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) cnt[q] = 0;
+    double min_margin = __longlong_as_double(0x7ff0000000000000ll);
+    bool risky = false;
     const int min_ci = n_cap < n_img ? n_cap : n_img;
     const int nk = Dp / KC;
 
@@ -165,6 +207,12 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
             const bool row_cap = gm < n_cap;
             const int li = row_cap ? gm : gm - n_cap;
             const double dc = (is_test && li < min_ci) ? dcross_sm[gm] : 0.0;
+            // tolerance of this row's distance differences (0 without the guard); a bound that is not small against
+            // the row itself, or not finite, sends the centre to the float64 kernels as well
+            const double tol = tolc_sm[gm] / sqrt(nrm_sm[gm]);
+            if (tolc_sm[gm] != 0.0 && !(tol < 0.05)) risky = true;
+            const int own = is_test ? gm : (is_std_im ? gm : n_test + (gm - RAW_ROW0));        // the row's own candidate
+            const int cross = row_cap ? n_cap + li : li;
 #pragma unroll
             for (int j = 0; j < 2; ++j)
 #pragma unroll
@@ -174,13 +222,31 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
                     if (is_test) {
                         if (n >= n_test) continue;
                         const bool col_cap = n < n_cap;
-                        if (col_cap == row_cap) cnt[row_cap ? 0 : 1] += ds < dv;
-                        else if (li < min_ci) cnt[row_cap ? 2 : 3] += dc < dv;
+                        if (col_cap == row_cap) {
+                            cnt[row_cap ? 0 : 1] += ds < dv;
+                            if (n != own) {
+                                const double m = fabs(ds - dv);
+                                min_margin = fmin(min_margin, m);
+                                risky |= m <= tol;
+                            }
+                        } else if (li < min_ci) {
+                            cnt[row_cap ? 2 : 3] += dc < dv;
+                            if (n != cross) {
+                                const double m = fabs(dc - dv);
+                                min_margin = fmin(min_margin, m);
+                                risky |= m <= tol;
+                            }
+                        }
                     } else {
                         if (n >= n_eval) continue;
                         const int base = is_std_im ? 4 : 6;
                         if (n >= n_test) cnt[base] += ds < dv;
                         cnt[base + 1] += ds < dv;
+                        if (n != own) {
+                            const double m = fabs(ds - dv);
+                            min_margin = fmin(min_margin, m);
+                            risky |= m <= tol;
+                        }
                     }
                 }
         }
@@ -193,7 +259,14 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
         for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
         if (lane == 0 && c) atomicAdd(&cnt_sm[q], c);
     }
+    if (__any_sync(0xffffffffu, risky) && lane == 0) risky_sm = 1;
+    for (int o = 16; o; o >>= 1) min_margin = fmin(min_margin, __shfl_xor_sync(0xffffffffu, min_margin, o));
+    if (lane == 0) atomicMin(&margin_sm, (unsigned long long)__double_as_longlong(min_margin));     // non-negative doubles order like integers
     __syncthreads();
+    if (tid == 0) {
+        if (prm.margin_out) prm.margin_out[task.centre] = __longlong_as_double((long long)margin_sm);
+        if (prm.amp2 && risky_sm && prm.reroute_list) prm.reroute_list[atomicAdd(prm.reroute_count, 1)] = task_id;
+    }
     if (tid < 8) {
         const long den_cc = (long)n_cap * n_cap - n_cap, den_ii = (long)n_img * n_img - n_img;
         const long den_x = (long)n_cap * n_img - min_ci;
@@ -209,6 +282,7 @@ cudaError_t launch_score(const ScoreParams& p, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     if (p.n_cap + p.n_img + p.n_im > EVAL_PAD - 1 || p.n_im > YHAT_ROWS - EVAL_PAD || p.Dp % KC != 0)
         return cudaErrorInvalidValue;
+    if (p.n_tasks <= 0) return cudaSuccess;
     score_kernel<<<p.n_tasks, THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }

@@ -2,7 +2,8 @@
 
 File loading (GIfTI betas, pickled embeddings; data.py:345-503) is out of scope — the dataset is not on these
 boxes — and is replaced by `multimodal_decoding_b200.synthetic`, which produces arrays with the same contracts.
-The standardisation helpers are one-pass host pre-steps and stay on the host in numpy float64.
+The standardisation helpers are one-pass host pre-steps and stay on the host; they restate sklearn's
+StandardScaler arithmetic including its dtype rule (float32 in -> float32 out), pinned by tests/golden/data_cases.npz.
 """
 from __future__ import annotations
 
@@ -25,21 +26,58 @@ TEST_BATCH_SIZE = NUM_TEST_STIMULI
 SELECT_DEFAULT = "default"
 
 
+_FLOAT_DTYPES = (np.float64, np.float32, np.float16)
+
+
+def _as_float(a):
+    """sklearn's input validation for the scaler (dtype=FLOAT_DTYPES): float arrays keep their dtype, the rest -> float64."""
+    a = np.asarray(a)
+    return a if a.dtype in _FLOAT_DTYPES else a.astype(np.float64)
+
+
 def _fit_scaler(train):
-    """StandardScaler().fit semantics: population std (ddof=0), zero-variance columns keep scale 1."""
-    train = np.asarray(train, dtype=np.float64)
-    mean = train.mean(axis=0)
-    scale = train.std(axis=0)
-    scale[scale == 0.0] = 1.0
+    """StandardScaler().fit (data.py:507, 526) restated: sklearn's corrected two-pass variance with float64
+    accumulators whatever the input dtype (`_incremental_mean_and_var` on a first batch), population variance, and
+    scale 1 for the features `_is_constant_feature` cannot tell from a constant."""
+    X = _as_float(train)
+    nan_mask = np.isnan(X)
+    sum_op = np.nansum if nan_mask.any() else np.sum
+    acc = {"dtype": np.float64} if X.dtype.itemsize < 8 else {}
+    new_sum = sum_op(X, axis=0, **acc)
+    count = X.shape[0] - sum_op(nan_mask.astype(X.dtype), axis=0, **acc)
+    count = np.asarray(count, dtype=np.float64)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        mean = new_sum / count
+        temp = X - mean                      # float64: `mean` is
+        correction = sum_op(temp, axis=0)
+        temp **= 2
+        unnormalized = sum_op(temp, axis=0)
+        unnormalized -= correction ** 2 / count
+        var = unnormalized / count
+    n_seen = count[0] if count.size and count.max() == count.min() else count
+    eps = np.finfo(np.float64).eps
+    constant = var <= n_seen * eps * var + (n_seen * mean * eps) ** 2
+    scale = np.sqrt(var)
+    scale[constant] = 1.0
     return mean, scale
+
+
+def _transform(a, mean, scale):
+    """StandardScaler.transform: a copy in the input's own float dtype, centred and scaled IN that dtype (float32
+    betas / latents stay float32, as in the reference; the fp16 cast of searchlight.py:247-248 then rounds the same
+    values)."""
+    X = np.array(_as_float(a), copy=True)
+    X -= mean.astype(X.dtype)
+    X /= scale.astype(X.dtype)
+    return X
 
 
 def standardize_latents(train_latents, test_latents, imagery_latents=None):
     """data.py:506-515: z-score every split with the TRAIN statistics."""
     mean, scale = _fit_scaler(train_latents)
-    out = [(np.asarray(a, dtype=np.float64) - mean) / scale for a in (train_latents, test_latents)]
+    out = [_transform(a, mean, scale) for a in (train_latents, test_latents)]
     if imagery_latents is not None:
-        out.append((np.asarray(imagery_latents, dtype=np.float64) - mean) / scale)
+        out.append(_transform(imagery_latents, mean, scale))
     return tuple(out)
 
 
@@ -51,7 +89,7 @@ def standardize_fmri_betas(train_fmri_betas, test_fmri_betas, imagery_fmri_betas
     if imagery_fmri_betas is not None:
         splits.append(imagery_fmri_betas[:, keep])
     mean, scale = _fit_scaler(splits[0])
-    out = tuple((np.asarray(a, dtype=np.float64) - mean) / scale for a in splits)
+    out = tuple(_transform(a, mean, scale) for a in splits)
     print('done.')
     return out
 

@@ -281,6 +281,20 @@ class Engine:
         """0 = guard mode is on and detects a one-byte overrun on either side; -1 = guard mode off."""
         return int(self._lib.mmd_guard_selftest(self._h))
 
+    def set_predict_mode(self, mode: int):
+        """1 (default): predictions on the tcgen05 tensor cores (int8 digit GEMM, guarded); 0: float64 DMMA kernel.
+        Call before upload()."""
+        self._check(self._lib.mmd_set_predict_mode(self._h, int(mode)))
+
+    def enable_margins(self, on=True):
+        self._check(self._lib.mmd_enable_margins(self._h, 1 if on else 0))
+
+    def margins(self, n_centres: int) -> np.ndarray:
+        """Per centre: smallest |d(own candidate) - d(other candidate)| over the comparisons of the last searchlight call."""
+        out = np.empty(n_centres, dtype=np.float64)
+        self._check(self._lib.mmd_get_margins(self._h, out.ctypes.data_as(C.c_void_p), int(n_centres)))
+        return out
+
     # -- statistics --------------------------------------------------------------------------
     def reset_stats(self):
         self._lib.mmd_reset_stats(self._h)
@@ -290,9 +304,9 @@ class Engine:
         launches, clusters, flops = C.c_int64(), C.c_int64(), C.c_double()
         self._check(self._lib.mmd_get_stats(self._h, ms, C.byref(launches), C.byref(clusters), C.byref(flops)))
         names = [self._lib.mmd_stage_name(i).decode() for i in range(_lib.N_STAGES)]
-        cnt, solve = (C.c_int64 * 6)(), C.c_double()
+        cnt, solve = (C.c_int64 * _lib.N_COUNTERS)(), C.c_double()
         self._check(self._lib.mmd_get_counters(self._h, cnt, C.byref(solve)))
         return {"stage_ms": dict(zip(names, [float(x) for x in ms])), "launches": launches.value,
                 "clusters": clusters.value, "syrk_flops": flops.value, "batches": cnt[0], "core_tasks": cnt[1],
                 "grouped_centres": cnt[2], "sum_shared_prefix": cnt[3], "host_plan_ms": cnt[4] / 1e3,
-                "host_adjacency_h2d_ms": cnt[5] / 1e3, "solve_flops": solve.value}
+                "host_adjacency_h2d_ms": cnt[5] / 1e3, "rerouted_centres": cnt[6], "solve_flops": solve.value}
