@@ -128,6 +128,23 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
                          const int32_t* perm_test, const int32_t* perm_imagery, int n_perm, double* scores_out,
                          int32_t* flags_out, double* null_out);
 
+/* Alpha grid x K-fold cross-validation per neighbourhood: what
+ *   GridSearchCV(Ridge(fit_intercept=False), param_grid=dict(alpha=alphas), scoring=make_scorer(pairwise_accuracy), cv=n_folds)
+ * (ridge_regression_decoding.py:111-117) computes in cv_results_["split<f>_test_score"] when it is fitted on the training
+ * trials of one centre, X[train_ids][:, adjacency[i]] -> latents[train_ids] (BASELINE.json north_star (3)).
+ *   alphas        (n_alphas) float64 > 0, HOST
+ *   fold_bounds   (n_folds + 1) int32, HOST: fold f holds the training trials at positions fold_bounds[f] ..
+ *                 fold_bounds[f+1]-1 of train_ids (KFold without shuffling, sklearn/model_selection/_split.py: the first
+ *                 n_train % n_folds folds have one trial more)
+ *   fold_scores_out (n_centres x n_alphas x n_folds) float64, HOST: pairwise_accuracy(latents_val, predictions_val)
+ *                 (eval.py:116-123, cosine, no standardisation) of the ridge fitted without the fold
+ * The caller averages over the folds, takes the first best alpha (GridSearchCV's rank rule) and refits with
+ * mmd_searchlight; the Python mirror does exactly that (custom_search_light with a GridSearchCV estimator).
+ * Per cluster of centres the Gram of every fold's trials is computed once and subtracted inside the per-centre gather
+ * (A = G - G_f + alpha I); the validation trials run through the solver in chunks of 144 right-hand sides. */
+int mmd_searchlight_cv(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, const double* alphas, int n_alphas,
+                       const int32_t* fold_bounds, int n_folds, double* fold_scores_out, int32_t* flags_out);
+
 /* eval.py primitives for arbitrary shapes, HOST float64 row-major buffers.
  *   mmd_cosine_distances          get_distance_matrix(predictions, originals, "cosine")   eval.py:103-104
  *   mmd_dist_mat_to_pairwise_acc  dist_mat_to_pairwise_acc(dist_mat)                      eval.py:107-113

@@ -65,6 +65,50 @@ def _estimator_alpha(estimator) -> float:
     return float(alpha)
 
 
+def _grid_search_spec(estimator):
+    """(alphas, n_splits) when `estimator` is GridSearchCV(Ridge(fit_intercept=False), param_grid=dict(alpha=[...]), cv=int)
+    -- the construction of ridge_regression_decoding.py:111-117 -- else None."""
+    if not (hasattr(estimator, "param_grid") and hasattr(estimator, "estimator")):
+        return None
+    grid = estimator.param_grid
+    if not isinstance(grid, dict) or set(grid) != {"alpha"}:
+        raise ValueError("the searchlight grid search varies `alpha` only (param_grid=dict(alpha=[...]))")
+    if getattr(estimator.estimator, "fit_intercept", False):
+        raise ValueError("the searchlight path fits without intercept (searchlight.py:240); got fit_intercept=True")
+    alphas = [float(a) for a in grid["alpha"]]
+    if not alphas or not all(a > 0.0 for a in alphas):
+        raise ValueError("param_grid['alpha'] must hold positive values")
+    cv = getattr(estimator, "cv", None)
+    n_splits = 5 if cv is None else cv                 # sklearn's default
+    if not isinstance(n_splits, (int, np.integer)):
+        raise ValueError("cv must be an integer number of contiguous folds (KFold without shuffling)")
+    return alphas, int(n_splits)
+
+
+def search_light_cv(eng, A, alphas, n_splits, n_train):
+    """Per-centre GridSearchCV on the uploaded problem: returns (scores (n, 8) of the refitted best alpha, flags,
+    best_alpha (n,), mean_test_score (n, n_alphas)).  Fold scores come from `mmd_searchlight_cv`; the mean over the folds
+    and the first-best rule (GridSearchCV: rank "min" of the mean test score, first index of rank 1) are applied here with
+    numpy as sklearn does; the refit runs one fixed-alpha searchlight per selected alpha."""
+    from ..ridge_regression_decoding import kfold_bounds
+    A = _require_rectangular(A, "the cross-validated searchlight")
+    if n_train < n_splits:
+        raise ValueError(f"Cannot have number of splits n_splits={n_splits} greater than the number of samples: "
+                         f"n_samples={n_train}.")
+    bounds = [0] + [hi for _, hi in kfold_bounds(n_train, n_splits)]
+    fold_scores, flags = eng.searchlight_cv(A, alphas, bounds)
+    mean = np.average(fold_scores, axis=2)             # _search.py: array_means = np.average(array, axis=1)
+    best_idx = np.argmax(mean, axis=1)
+    best_alpha = np.asarray(alphas, dtype=np.float64)[best_idx]
+    scores = np.empty((len(A), len(score_keys())), dtype=np.float64)
+    for i in np.unique(best_idx):
+        sel = np.flatnonzero(best_idx == i)
+        s, f = eng.searchlight(np.asarray(A)[sel], alphas[i])
+        scores[sel] = s
+        flags[sel] |= f
+    return scores, flags, best_alpha, mean
+
+
 def _as_f16(a, name):
     if hasattr(a, "data_ptr"):                        # torch tensor (possibly already on the GPU)
         import torch
@@ -137,12 +181,15 @@ def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *,
     """(n_centres x 8) float64 score block and per-centre flags for the centres in `A` on one GPU.
     `anchors` (ragged `A` only): the vertex each centre sits on, used to group nearby centres."""
     eng = get_engine(device)
-    alpha = _estimator_alpha(estimator)
+    grid = _grid_search_spec(estimator)
+    alpha = None if grid else _estimator_alpha(estimator)
     A = _rectangular(A)
     if upload:
         if is_caption is None:
             is_caption = _is_caption_mask(len(test_ids))
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption)
+    if grid:
+        return search_light_cv(eng, A, grid[0], grid[1], len(train_ids))[:2]
     if _is_ragged(A):
         return eng.searchlight_ragged(A, alpha, anchors)
     return eng.searchlight(A, alpha)

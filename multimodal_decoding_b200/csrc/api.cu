@@ -128,6 +128,28 @@ struct TimedSpan {
 
 }  // namespace
 
+// Cross-validation state of one mmd_searchlight_cv call (cv.cu): per-fold panels derived from the uploaded ones.
+struct CvState {
+    int n_folds = 0;
+    std::vector<int> lo, hi, ld;                    // fold f = training positions [lo, hi); ld = its padded length
+    std::vector<double> alphas;
+    std::vector<DevBuf> xfold, xty_tr, cand, cand_sq;      // per fold
+    std::vector<std::vector<DevBuf>> xe;                   // per fold and chunk of EVAL_PAD validation trials
+    DevBuf yfold, pool, counts, probs;
+    size_t pool_stride = 0;                         // doubles between the fold Gram pools of a batch
+    void release() {
+        for (auto* v : {&xfold, &xty_tr, &cand, &cand_sq})
+            for (DevBuf& b : *v) b.release();
+        for (auto& v : xe)
+            for (DevBuf& b : v) b.release();
+        yfold.release();
+        pool.release();
+        counts.release();
+        probs.release();
+        xfold.clear(); xty_tr.clear(); cand.clear(); cand_sq.clear(); xe.clear();
+    }
+};
+
 struct mmd_handle {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -149,6 +171,7 @@ struct mmd_handle {
     // integer prediction GEMM (predict_i8.cu): digit planes of XtY (per upload) and of every centre's Zt (per batch),
     // their scales, the score kernel's tolerance input, the list of centres handed back to the float64 kernels
     DevBuf xplanes, sX, colmax, zplanes, sZ, amp2, i8_status, reroute_list, reroute_counts, margins;
+    CvState* cv = nullptr;          // non-null while mmd_searchlight_cv runs
     int predict_mode = 1;           // 1: tcgen05 int8 digit GEMM + float64 reroute of guarded centres; 0: float64 DMMA kernel
     int n_sms = 148;
     int call_batches = 0;           // batches of the current searchlight call (index into reroute_counts)
@@ -488,6 +511,87 @@ int run_xty(mmd_handle* h) {
     return 0;
 }
 
+// Cross-validation part of a batch (after prep and the full union Grams): fold Grams, then for every fold, alpha and
+// chunk of validation trials: factor + solve without the fold, raw predictions, pairwise-accuracy counts.
+int run_batch_cv(mmd_handle* h, const SolveParams& base, const std::vector<GemmProblem>& probs, int n_tasks, int n_core, int kp,
+                 int sp_max, int max_u) {
+    CvState& cv = *h->cv;
+    const int n_cl = (int)probs.size(), n_alphas = (int)cv.alphas.size();
+    const double* pool0 = h->gram_pool.as<double>();
+    // fold Grams of every cluster union, same layout as the full Gram pool
+    CU(cv.probs.ensure((size_t)cv.n_folds * n_cl * sizeof(GemmProblem)));
+    std::vector<GemmProblem> fp((size_t)cv.n_folds * n_cl);
+    for (int f = 0; f < cv.n_folds; ++f)
+        for (int c = 0; c < n_cl; ++c) {
+            GemmProblem p = probs[c];
+            p.A = p.B = cv.xfold[f].as<__half>();
+            p.lda = p.ldb = cv.ld[f];
+            p.K = cv.ld[f];
+            p.C = cv.pool.as<double>() + (size_t)f * cv.pool_stride + (probs[c].C - pool0);
+            fp[(size_t)f * n_cl + c] = p;
+        }
+    CU(cudaMemcpyAsync(cv.probs.p, fp.data(), fp.size() * sizeof(GemmProblem), cudaMemcpyDefault, h->stream));
+    span_begin(h, ST_SYRK);
+    for (int f = 0; f < cv.n_folds; ++f)
+        CU(launch_gemm_gather(cv.probs.as<GemmProblem>() + (size_t)f * n_cl, n_cl, max_u, max_u, h->stream));
+    span_end(h, cv.n_folds);
+
+    PredictParams pp{};
+    pp.tasks = base.tasks;
+    pp.n_tasks = n_tasks;
+    pp.kp_max = kp;
+    pp.work = h->work.as<double>();
+    pp.Dp = h->Dp;
+    pp.yhat = h->yhat.as<double>();
+    pp.standardize = 0;
+    CvScoreParams cs{};
+    cs.tasks = base.tasks;
+    cs.n_tasks = n_tasks;
+    cs.yhat = h->yhat.as<double>();
+    cs.Dp = h->Dp;
+    cs.counts = cv.counts.as<unsigned long long>();
+    cs.count_stride = (long)n_alphas * cv.n_folds;
+    for (int f = 0; f < cv.n_folds; ++f) {
+        const int n_val = cv.hi[f] - cv.lo[f];
+        pp.XtY = cv.xty_tr[f].as<double>();
+        cs.cand = cv.cand[f].as<double>();
+        cs.cand_sq = cv.cand_sq[f].as<double>();
+        cs.n_cand = n_val;
+        for (int a = 0; a < n_alphas; ++a) {
+            cs.count_off = a * cv.n_folds + f;
+            for (size_t c = 0; c < cv.xe[f].size(); ++c) {
+                SolveParams sp = base;
+                sp.alpha = cv.alphas[a];
+                sp.Xe = cv.xe[f][c].as<__half>();
+                sp.gram_sub_off = (long)((cv.pool.as<double>() + (size_t)f * cv.pool_stride) - pool0);
+                span_begin(h, ST_SOLVE);
+                if (n_core > 0) {
+                    SolveParams cp = sp;
+                    cp.tasks = sp.tasks + n_tasks;
+                    cp.n_tasks = n_core;
+                    cp.kp_max = sp_max;
+                    cp.work = h->core_work.as<double>();
+                    cp.flags = h->group_flags.as<int>();
+                    cp.core_only = 1;
+                    CU(cudaMemsetAsync(h->group_flags.p, 0, (size_t)n_core * sizeof(int), h->stream));
+                    CU(launch_factor_solve(cp, h->stream));
+                }
+                CU(launch_factor_solve(sp, h->stream));
+                span_end(h, n_core > 0 ? 2 : 1);
+                span_begin(h, ST_PREDICT);
+                CU(launch_predict(pp, h->stream));
+                span_end(h);
+                cs.row0 = (int)c * EVAL_PAD;
+                cs.n_rows = std::min(EVAL_PAD, n_val - cs.row0);
+                span_begin(h, ST_SCORE);
+                CU(launch_cv_score(cs, h->stream));
+                span_end(h);
+            }
+        }
+    }
+    return 0;
+}
+
 // One batch = clusters [c0, c1).  `slot0` = first output slot when yhat_only (diagnostic) is set.
 int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1, int k_max, int kp, int sp_max,
               double alpha, bool with_null, bool raw_yhat) {
@@ -606,6 +710,8 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     sp.work = h->work.as<double>();
     sp.flags = h->flags.as<int>();
     sp.core_only = 0;
+    sp.gram_sub_off = 0;
+    if (h->cv) return run_batch_cv(h, sp, probs, n_tasks, n_core, kp, sp_max, max_u);
     span_begin(h, ST_SOLVE);
     if (n_core > 0) {
         SolveParams cp = sp;                                   // the shared cores first: factorisation + forward solve
@@ -781,6 +887,10 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
     CU(h->core_work.ensure(std::max<size_t>((size_t)max_core * (sp_max + EVAL_PAD) * sp_max, 1) * sizeof(double)));
     CU(h->group_flags.ensure(std::max<size_t>(max_core, 1) * sizeof(int)));
     if (with_null) CU(h->dist.ensure((size_t)max_tasks * NULL_DIST_ROWS * EVAL_PAD * sizeof(double)));
+    if (h->cv) {
+        h->cv->pool_stride = std::max(h->cv->pool_stride, max_pool);
+        CU(h->cv->pool.ensure((size_t)h->cv->n_folds * h->cv->pool_stride * sizeof(double)));
+    }
     if (h->predict_mode == 1 && !raw_yhat) {
         CU(h->zplanes.ensure((size_t)max_tasks * I8_DIGITS * EVAL_PAD * kp));
         CU(h->sZ.ensure((size_t)max_tasks * EVAL_PAD * sizeof(double)));
@@ -854,7 +964,7 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
                                 h->dist.bytes + h->gram_pool.bytes + h->zplanes.bytes;
             const double per_centre = 1.25 * (double)(kp + EVAL_PAD) * kp * sizeof(double) +
                                       (double)YHAT_ROWS * h->Dp * sizeof(double) + 2.5 * kp * sizeof(int) +
-                                      0.1 * (double)kp * kp * sizeof(double) +
+                                      0.1 * (double)kp * kp * sizeof(double) * (h->cv ? 1 + h->cv->n_folds : 1) +
                                       (with_null ? (double)NULL_DIST_ROWS * EVAL_PAD * sizeof(double) : 0.0) +
                                       (h->predict_mode == 1 ? (double)I8_DIGITS * EVAL_PAD * kp : 0.0);
             const double fit = 0.5 * ((double)free_b + (double)held) / per_centre;
@@ -1453,6 +1563,129 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
     release_upload_staging(h);
     if (collect_i8_stats(h)) return 1;
     return report_input_flags(h, bad, y_bad, "mmd_searchlight_null");
+}
+
+// GridSearchCV semantics per neighbourhood (ridge_regression_decoding.py:111-117; KFold without shuffling:
+// fold f = training positions fold_bounds[f] .. fold_bounds[f+1]-1 in train_ids order).  fold_scores_out is
+// (n_centres x n_alphas x n_folds): pairwise_accuracy(latents_val, predictions_val) of eval.py:115-123.
+int mmd_searchlight_cv(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, const double* alphas, int n_alphas,
+                       const int32_t* fold_bounds, int n_folds, double* fold_scores_out, int32_t* flags_out) {
+    if (!h) return 1;
+    if (!adjacency || !alphas || !fold_bounds || !fold_scores_out) return fail(h, "mmd_searchlight_cv: null pointer");
+    if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight_cv");
+    if (n_centres < 0 || n_alphas < 1 || n_alphas > 64) return fail(h, "mmd_searchlight_cv: need 1..64 alphas and a non-negative centre count");
+    if (n_folds < 2 || n_folds > h->n_train)
+        return fail(h, "mmd_searchlight_cv: k-fold cross-validation requires at least one train/test split by setting n_splits=2 "
+                       "or more and at most n_samples=%d, got n_splits=%d", h->n_train, n_folds);
+    if (fold_bounds[0] != 0 || fold_bounds[n_folds] != h->n_train) return fail(h, "mmd_searchlight_cv: fold bounds must run from 0 to n_train");
+    for (int f = 0; f < n_folds; ++f)
+        if (fold_bounds[f + 1] <= fold_bounds[f]) return fail(h, "mmd_searchlight_cv: empty fold %d", f);
+    for (int a = 0; a < n_alphas; ++a)
+        if (!(alphas[a] > 0.0)) return fail(h, "mmd_searchlight_cv: alpha must be positive (got %g)", alphas[a]);
+    if (n_centres == 0) return 0;
+    if (is_device_ptr(adjacency)) return fail(h, "mmd_searchlight_cv: adjacency must be a host pointer");
+    CU(cudaSetDevice(h->device));
+
+    CvState cv;
+    cv.n_folds = n_folds;
+    cv.alphas.assign(alphas, alphas + n_alphas);
+    cv.xfold.resize(n_folds);
+    cv.xty_tr.resize(n_folds);
+    cv.cand.resize(n_folds);
+    cv.cand_sq.resize(n_folds);
+    cv.xe.resize(n_folds);
+    int rc = 0;
+    auto prepare = [&]() -> int {
+        int ld_max = 0;
+        for (int f = 0; f < n_folds; ++f) {
+            cv.lo.push_back(fold_bounds[f]);
+            cv.hi.push_back(fold_bounds[f + 1]);
+            cv.ld.push_back(round_up(fold_bounds[f + 1] - fold_bounds[f], 64));
+            ld_max = std::max(ld_max, cv.ld.back());
+        }
+        CU(cv.yfold.ensure((size_t)h->Dp * ld_max * sizeof(__half)));
+        CU(cv.counts.ensure((size_t)n_centres * n_alphas * n_folds * sizeof(unsigned long long)));
+        CU(cudaMemsetAsync(cv.counts.p, 0, cv.counts.bytes, h->stream));
+        CU(cv.probs.ensure(sizeof(GemmProblem)));
+        span_begin(h, ST_XTY);
+        int launches = 0;
+        for (int f = 0; f < n_folds; ++f) {
+            const int lo = cv.lo[f], n_val = cv.hi[f] - lo, ld = cv.ld[f];
+            const int n_chunks = (n_val + EVAL_PAD - 1) / EVAL_PAD;
+            CU(cv.xfold[f].ensure((size_t)h->V * ld * sizeof(__half)));
+            CU(cv.xty_tr[f].ensure((size_t)h->V * h->Dp * sizeof(double)));
+            CU(cv.cand[f].ensure((size_t)n_chunks * EVAL_PAD * h->Dp * sizeof(double)));
+            CU(cv.cand_sq[f].ensure((size_t)n_chunks * EVAL_PAD * sizeof(double)));
+            CU(launch_copy_cols_f16(h->Xt.as<__half>(), h->ldt, lo, n_val, cv.xfold[f].as<__half>(), ld, h->V, h->stream));
+            CU(launch_copy_cols_f16(h->Yt.as<__half>(), h->ldt, lo, n_val, cv.yfold.as<__half>(), ld, h->Dp, h->stream));
+            // XtY without the fold: XtY - Xfold Yfold^T
+            GemmProblem p{};
+            p.A = cv.xfold[f].as<__half>();
+            p.lda = ld;
+            p.M = h->V;
+            p.B = cv.yfold.as<__half>();
+            p.ldb = ld;
+            p.N = h->Dp;
+            p.K = ld;
+            p.C = cv.xty_tr[f].as<double>();
+            p.ldc = h->Dp;
+            CU(cudaMemcpyAsync(cv.probs.p, &p, sizeof(p), cudaMemcpyDefault, h->stream));
+            CU(launch_gemm_gather(cv.probs.as<GemmProblem>(), 1, p.M, p.N, h->stream));
+            CU(launch_rsub(h->XtY.as<double>(), cv.xty_tr[f].as<double>(), (long)h->V * h->Dp, h->stream));
+            CU(launch_fold_latents(h->Yt.as<__half>(), h->ldt, lo, n_val, n_chunks * EVAL_PAD, h->Dp, cv.cand[f].as<double>(),
+                                   cv.cand_sq[f].as<double>(), h->stream));
+            cv.xe[f].resize(n_chunks);
+            for (int c = 0; c < n_chunks; ++c) {
+                CU(cv.xe[f][c].ensure((size_t)h->V * EVAL_PAD * sizeof(__half)));
+                CU(launch_copy_cols_f16(h->Xt.as<__half>(), h->ldt, lo + c * EVAL_PAD, std::min(EVAL_PAD, n_val - c * EVAL_PAD),
+                                        cv.xe[f][c].as<__half>(), EVAL_PAD, h->V, h->stream));
+            }
+            launches += 5 + n_chunks;
+            CU(cudaStreamSynchronize(h->stream));          // `p` is a stack object; the fold panels are ready behind this point
+        }
+        span_end(h, launches);
+        return 0;
+    };
+    rc = prepare();
+    if (!rc) {
+        h->cv = &cv;
+        const Rows rows{adjacency, nullptr, k, nullptr, n_centres};
+        rc = run_searchlight(h, rows, cv.alphas[0], false, true);
+        h->cv = nullptr;
+    }
+    std::vector<unsigned long long> counts;
+    int bad = 0, y_bad = 0;
+    if (!rc) {
+        counts.resize((size_t)n_centres * n_alphas * n_folds);
+        auto fetch = [&]() -> int {
+            CU(cudaMemcpyAsync(&bad, h->misc_flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaMemcpyAsync(&y_bad, h->y_bad.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaMemcpyAsync(counts.data(), cv.counts.p, counts.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+            if (flags_out) CU(cudaMemcpyAsync(flags_out, h->flags.p, (size_t)n_centres * sizeof(int), cudaMemcpyDefault, h->stream));
+            return 0;
+        };
+        rc = fetch();
+    }
+    cudaStreamSynchronize(h->stream);
+    if (rc) {
+        h->spans.clear();
+        h->events_used = 0;
+    } else {
+        resolve_spans(h);
+        release_upload_staging(h);
+    }
+    cv.release();
+    if (rc) return rc;
+    if ((rc = report_input_flags(h, bad, y_bad, "mmd_searchlight_cv"))) return rc;
+    for (int i = 0; i < n_centres; ++i)
+        for (int a = 0; a < n_alphas; ++a)
+            for (int f = 0; f < n_folds; ++f) {
+                const long n_val = fold_bounds[f + 1] - fold_bounds[f];
+                const long den = n_val * n_val - n_val;                 // dist_mat.size - diag.size (eval.py:111)
+                const size_t o = ((size_t)i * n_alphas + a) * n_folds + f;
+                fold_scores_out[o] = den > 0 ? (double)counts[o] / (double)den : std::nan("");
+            }
+    return 0;
 }
 
 // ---- eval.py primitives on arbitrary shapes (host float64 buffers) ----

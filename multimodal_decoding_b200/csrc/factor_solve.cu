@@ -290,6 +290,19 @@ __device__ __forceinline__ void strip_init(Frag<NBW>& acc, const CentreTask& tas
                     const int hi = a > b ? a : b, lo = a > b ? b : a;
                     acc.v[i][nb][q] = __ldg(task.gram + (long)hi * task.gram_ld + lo);
                 }
+        if (prm.gram_sub_off != 0) {                       // cross-validation: leave out the fold's trials
+            const double* gsub = task.gram + prm.gram_sub_off;
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int nb = 0; nb < NBW; ++nb)
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int a = li[i] >= 0 ? li[i] : 0, b = lj[nb][q] >= 0 ? lj[nb][q] : 0;
+                        const int hi = a > b ? a : b, lo = a > b ? b : a;
+                        acc.v[i][nb][q] -= __ldg(gsub + (long)hi * task.gram_ld + lo);
+                    }
+        }
 #pragma unroll
         for (int i = 0; i < 2; ++i)
 #pragma unroll
@@ -556,7 +569,7 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
     }
 
     if (prm.core_only) {
-        if (tid == 0) prm.flags[task.centre] = bad_pivot;
+        if (tid == 0 && bad_pivot) prm.flags[task.centre] = 1;     // the caller zeroes the flags
         return;
     }
 
@@ -608,7 +621,7 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         __syncthreads();                                         // Zt block visible before it is read as an operand
     }
     if (tid == 0 && task.core_flag && *task.core_flag) bad_pivot = 1;
-    if (tid == 0) prm.flags[task.centre] = bad_pivot;
+    if (tid == 0 && bad_pivot) prm.flags[task.centre] = 1;         // zeroed by the caller; sticky over the launches of a call
 }
 
 }  // namespace

@@ -58,6 +58,8 @@ struct SolveParams {
     double* work;         // per task: (task.kp + EVAL_PAD) x task.kp doubles at the start of its stride
     int* flags;           // per task slot: 1 if a non-positive pivot was met
     int core_only;        // 1: tasks are shared cores: factorisation + forward solve only (no backward solve)
+    long gram_sub_off;    // 0, or the offset (in doubles) from task.gram to a second Gram of the same layout that is subtracted:
+                          // A = G[loc,loc] - G_f[loc,loc] + alpha I, the normal matrix without the trials of fold f (cv.cu)
 };
 size_t factor_solve_smem_bytes();
 cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s);
@@ -162,6 +164,29 @@ cudaError_t launch_standardize_columns(double* A, int n, int D, long ld, cudaStr
 cudaError_t launch_cosine_dist(const double* P, int np, const double* C, int nc, int D, long ld, double* psq, double* csq,
                                double* dist, cudaStream_t s);
 cudaError_t launch_pairwise_count(const double* dist, int r, int c, unsigned long long* count, cudaStream_t s);
+
+// ---- cv.cu ------------------------------------------------------------------------------
+struct CvScoreParams {
+    const CentreTask* tasks;
+    int n_tasks;
+    const double* yhat;        // per task YHAT_ROWS x Dp raw predictions; rows 0..n_rows-1 = the chunk's validation trials
+    int Dp;
+    const double* cand;        // (n_cand rounded up to EVAL_PAD) x Dp: the fold's latents as float64, zero rows below
+    const double* cand_sq;     // their squared norms
+    int n_cand;                // validation trials of the fold
+    int row0;                  // first validation trial of the chunk (multiple of EVAL_PAD)
+    int n_rows;                // trials of the chunk (<= EVAL_PAD)
+    unsigned long long* counts;   // counts[task.centre * count_stride + count_off] += #{(i, j): d[i][own(i)] < d[i][j]}
+    long count_stride;
+    int count_off;
+};
+size_t cv_score_smem_bytes();
+cudaError_t launch_cv_score(const CvScoreParams& p, cudaStream_t s);
+cudaError_t launch_copy_cols_f16(const __half* src, long ld_src, int col0, int n_cols, __half* dst, int ld_dst, long n_rows,
+                                 cudaStream_t s);
+cudaError_t launch_rsub(const double* a, double* inout, long n, cudaStream_t s);
+cudaError_t launch_fold_latents(const __half* Yt, long ldy, int col0, int n_rows, int n_rows_pad, int Dp, double* cand, double* sq,
+                                cudaStream_t s);
 
 // ---- prep.cu -----------------------------------------------------------------------------
 // task t reads its neighbour list adjacency[task_row_off[t] .. + task_k[t]) and writes kp_max-strided rows

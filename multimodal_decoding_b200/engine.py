@@ -174,6 +174,21 @@ class Engine:
         self._check(fn(self._h, adj.ctypes.data, n, k, float(alpha), scores.ctypes.data, flags.ctypes.data))
         return scores, flags
 
+    def searchlight_cv(self, adjacency, alphas, fold_bounds):
+        """Alpha grid x K-fold cross-validation per centre (mmd_searchlight_cv): returns (fold_scores (n, n_alphas,
+        n_folds), flags (n,)).  `fold_bounds`: n_folds + 1 positions into train_ids (contiguous folds, KFold order)."""
+        adj = np.ascontiguousarray(np.asarray(adjacency, dtype=np.int32))
+        if adj.ndim != 2:
+            raise ValueError("adjacency must be rectangular (n_centres, k)")
+        al = np.ascontiguousarray(np.asarray(alphas, dtype=np.float64))
+        fb = np.ascontiguousarray(np.asarray(fold_bounds, dtype=np.int32))
+        n, k = adj.shape
+        out = np.empty((n, len(al), len(fb) - 1), dtype=np.float64)
+        flags = np.zeros(n, dtype=np.int32)
+        self._check(self._lib.mmd_searchlight_cv(self._h, adj.ctypes.data, n, k, al.ctypes.data, len(al), fb.ctypes.data,
+                                                 len(fb) - 1, out.ctypes.data, flags.ctypes.data))
+        return out, flags
+
     def searchlight_null(self, adjacency, alpha, perm_test, perm_imagery):
         """Scores plus the null-distribution scores (searchlight.py:61-79) for target permutations given as index
         arrays into the test / imagery trials; returns (scores (n,8), flags (n,), null (n, n_perm, 6))."""

@@ -262,10 +262,10 @@ def kfold_bounds(n: int, n_splits: int = 5):
     return list(zip(ends - sizes, ends))
 
 
-def grid_search_ridge(x, y, alphas, n_splits: int = 5, dtype=np.float64):
-    """GridSearchCV(Ridge(fit_intercept=False), alpha grid, scoring=pairwise_accuracy, cv=5, refit).
-    Fold score = pairwise accuracy of un-standardised validation predictions; mean over folds;
-    first alpha in grid order wins ties.  Returns (best_alpha, mean_scores, W_refit)."""
+def grid_search_fold_scores(x, y, alphas, n_splits: int = 5, dtype=np.float64):
+    """cv_results_["split<f>_test_score"] of GridSearchCV(Ridge(fit_intercept=False), alpha grid,
+    scoring=make_scorer(pairwise_accuracy), cv=n_splits) (ridge_regression_decoding.py:111-117): (n_alphas x n_splits);
+    fold score = pairwise accuracy of the un-standardised validation predictions (eval.py:116-123)."""
     x = np.asarray(x, dtype=dtype)
     y = np.asarray(y, dtype=dtype)
     n = len(x)
@@ -275,6 +275,13 @@ def grid_search_ridge(x, y, alphas, n_splits: int = 5, dtype=np.float64):
         for a, alpha in enumerate(alphas):
             w = ridge_fit(x[tr], y[tr], alpha)
             scores[a, f] = pairwise_accuracy(y[lo:hi], np.asarray(x[lo:hi], dtype=np.float64) @ w, False)
+    return scores
+
+
+def grid_search_ridge(x, y, alphas, n_splits: int = 5, dtype=np.float64):
+    """GridSearchCV(..., refit): mean over folds; first alpha in grid order wins ties.
+    Returns (best_alpha, mean_scores, W_refit)."""
+    scores = grid_search_fold_scores(x, y, alphas, n_splits, dtype)
     mean = scores.mean(1)
     best = int(np.argmax(mean))                 # argmax returns the first maximum
-    return alphas[best], mean, ridge_fit(x, y, alphas[best])
+    return alphas[best], mean, ridge_fit(np.asarray(x, dtype=dtype), np.asarray(y, dtype=dtype), alphas[best])

@@ -99,6 +99,29 @@ def test_non_contiguous_trial_ids_and_stim_order(engine):
     assert np.array_equal(got, want)
 
 
+def test_config2_shapes_match_reference_fixture(engine, golden_dir):
+    """Headline shapes (k=750, N_train=4000, D=1024, smooth betas): 48 centres scored by the UNMODIFIED reference's
+    custom_search_light + sklearn Ridge (tests/golden/make_golden_r2.py -> searchlight_config2.npz).  The fixture stores
+    seeds, adjacency rows and scores; the inputs are regenerated and their checksums compared first."""
+    import hashlib
+    from multimodal_decoding_b200 import synthetic as syn
+    g = np.load(os.path.join(golden_dir, "searchlight_config2.npz"))
+    mesh = syn.make_mesh(level=int(g["cfg_level"]), seed=int(g["cfg_mesh_seed"]))
+    trials = syn.make_trials(mesh, n_train=int(g["cfg_n_train"]), n_dims=int(g["cfg_n_dims"]), seed=int(g["cfg_trial_seed"]))
+    inp = syn.make_searchlight_inputs(mesh, trials)
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    assert sha(inp.X) == str(g["x_sha256"]) and sha(inp.latents) == str(g["latents_sha256"])
+    is_cap = orc.default_is_caption(len(inp.test_ids))
+    engine.upload(inp.X, inp.latents, inp.train_ids, inp.test_ids, inp.imagery_ids, is_cap)
+    # neighbour rows: the engine's k-NN reproduces sklearn's rows bit for bit
+    dist, A = engine.knn(inp.coords, int(g["cfg_k"]))
+    assert np.array_equal(A[g["centres"]], g["adjacency"].astype(np.int64))
+    got, flags = engine.searchlight(g["adjacency"], float(g["cfg_alpha"]))
+    assert flags.sum() == 0
+    assert np.abs(got - g["scores"]).max() <= TOL
+    assert np.array_equal(got, g["scores"])
+
+
 def test_medium_k750_against_oracle(engine):
     """Full-size neighbourhoods (k=750, N_train=4000, D=1024) on a 10k-vertex mesh: a sample of centres is
     checked against the oracle; margins show the comparisons are not at rounding level."""

@@ -152,3 +152,18 @@ def test_group_stats_oracle_matches_reference(golden_dir):
         assert np.array_equal(so.tfce(t, edges, h=1, e=0.5, dh=0.2), g[f"{hemi}_tfce_h1_e05_dh02"])
         assert np.array_equal(so.tfce(t, edges, dh=0), g[f"{hemi}_tfce_auto"])
     assert not so.tfce(-np.abs(g["left_t"]), g["left_edges"]).any() and not g["left_tfce_nonpositive"].any()
+
+
+def test_oracle_per_centre_grid_search_matches_gridsearchcv(golden_dir):
+    """searchlight_cv.npz: sklearn GridSearchCV per neighbourhood (make_golden_r2.py); the oracle's fold scores give the
+    same mean test scores and the same selected alpha."""
+    g = np.load(os.path.join(golden_dir, "searchlight_cv.npz"))
+    ntr = int(g["n_train"])
+    X, Y = g["X"].astype(np.float64), g["latents"].astype(np.float64)
+    alphas = [float(a) for a in g["alphas"]]
+    for i in range(0, len(g["centres"]), 8):
+        nb = g["adjacency"][g["centres"][i]]
+        fs = orc.grid_search_fold_scores(X[:ntr][:, nb], Y[:ntr], alphas, int(g["n_folds"]))
+        mean = np.average(fs, axis=1)
+        assert np.array_equal(mean, g["mean_test_score"][i])
+        assert alphas[int(np.argmax(mean))] == g["best_alpha"][i]
