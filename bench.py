@@ -49,10 +49,11 @@ def parse_args():
     p.add_argument("--n-dims", type=int, default=1024)
     p.add_argument("--centres-per-step", type=int, default=0,
                    help="centres per step and GPU; 0 = the whole hemisphere (weak) or the rank's whole shard (strong)")
-    p.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                   help="weak: every GPU runs one whole hemisphere job per step (configs[4] distributes whole "
-                        "searchlights); strong: ONE hemisphere, centres sharded across the GPUs")
-    p.add_argument("--cpu-centres", type=int, default=1024, help="centres of the CPU-baseline sample")
+    p.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                   help="N > 1 only.  strong (default, north_star (5)): ONE hemisphere, centres sharded across the GPUs, the "
+                        "replica layout measured beside it; weak: every GPU runs one whole hemisphere job per step")
+    p.add_argument("--no-replicas", action="store_true", help="strong scaling: skip the replica-layout measurement")
+    p.add_argument("--cpu-centres", type=int, default=768, help="centres of the CPU-baseline sample")
     p.add_argument("--batch-centres", type=int, default=0, help="engine knob: centres per kernel batch (0 = default)")
     p.add_argument("--cluster-size", type=int, default=0, help="engine knob: centres per union-Gram cluster (0 = default)")
     p.add_argument("--group-size", type=int, default=0, help="engine knob: centres per prefix-sharing group (1 = off, 0 = default)")
@@ -201,6 +202,75 @@ def cpu_centres_per_sec(X, Y, A_rows, ids, n_centres, budget_s=30.0):
     return done / dt, done, dt, arm.cores
 
 
+SCORE_KEYS = ("pairwise_acc_captions", "pairwise_acc_images", "pairwise_acc_cross_captions_to_images",
+              "pairwise_acc_cross_images_to_captions", "pairwise_acc_imagery", "pairwise_acc_imagery_whole_test_set",
+              "pairwise_acc_imagery_no_std", "pairwise_acc_imagery_whole_test_set_no_std")
+
+
+def reference_available():
+    from baseline import make_ref
+    return make_ref.available()
+
+
+class RefArm:
+    """The UNMODIFIED reference (baseline/_ref, copied from /root/reference by baseline/make_ref.py at build time):
+    custom_search_light(X16, Y16, Ridge(alpha=1, fit_intercept=False), A[sample], ...) -> joblib over chunks of centres ->
+    sklearn Ridge.fit / predict + eval.py scoring, on the full-width X of the workload (the strided column gather of
+    searchlight.py:110 is paid).  X is handed over as a read-only np.memmap so that joblib passes it to its workers by
+    reference instead of dumping 1.4 GB per call (a per-call cost the real 164k-centre run amortises)."""
+
+    def __init__(self, X, Y, ids):
+        import tempfile
+        from baseline import make_ref
+        self.sl = make_ref.activate()
+        base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+        self.dir = tempfile.mkdtemp(prefix="mmd_ref_", dir=base)
+        path = os.path.join(self.dir, "X.npy")
+        np.save(path, np.asarray(X))
+        self.X = np.load(path, mmap_mode="r")
+        self.Y = np.ascontiguousarray(Y)
+        self.ids = [list(map(int, i)) for i in ids]
+        self.cores = host_cores()
+        import sklearn
+        self.versions = f"sklearn {sklearn.__version__}, numpy {np.__version__}"
+        try:
+            from threadpoolctl import threadpool_info
+            self.blas = ", ".join(sorted({f"{i.get('internal_api')} {i.get('version')}" for i in threadpool_info()
+                                          if i.get("user_api") == "blas"})) or "unknown"
+        except Exception:
+            self.blas = "unknown"
+
+    def close(self):
+        import shutil
+        del self.X
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+    def run(self, A_rows, n_jobs):
+        from sklearn.linear_model import Ridge
+        out = self.sl.custom_search_light(self.X, self.Y, estimator=Ridge(alpha=1.0, fit_intercept=False), A=np.asarray(A_rows),
+                                          train_ids=self.ids[0], test_ids=self.ids[1], imagery_ids=self.ids[2], n_jobs=n_jobs)
+        return np.array([[d[k] for k in SCORE_KEYS] for d in out], dtype=np.float64)
+
+
+def reference_centres_per_sec(arm, A_rows, n_centres):
+    """The reference both ways BASELINE.md section 4 names: n_jobs = cores (its default layout) and n_jobs = 1 with the BLAS
+    threads; returns the better rate, its description and the scores of the joblib run (the parity sample)."""
+    n = min(n_centres, len(A_rows))
+    arm.run(A_rows[:2 * arm.cores], arm.cores)                    # start the loky workers (they import torch via data.py)
+    t0 = time.perf_counter()
+    scores = arm.run(A_rows[:n], arm.cores)
+    dt_jobs = time.perf_counter() - t0
+    n1 = min(n, max(8, int(n / arm.cores)))
+    t0 = time.perf_counter()
+    arm.run(A_rows[:n1], 1)
+    dt_one = time.perf_counter() - t0
+    rate_jobs, rate_one = n / dt_jobs, n1 / dt_one
+    desc = (f"unmodified custom_search_light + sklearn Ridge(alpha=1) on {n} consecutive centres of the same workload, "
+            f"full-width X: n_jobs={arm.cores} -> {rate_jobs:.1f} centres/s ({dt_jobs:.1f} s); n_jobs=1 with BLAS threads on "
+            f"{n1} centres -> {rate_one:.1f} centres/s; the better one is reported ({arm.versions}, BLAS {arm.blas})")
+    return max(rate_jobs, rate_one), desc, scores
+
+
 # ----------------------------------------------------------------------------------------------------------
 # roofline bookkeeping
 # ----------------------------------------------------------------------------------------------------------
@@ -303,24 +373,25 @@ def knn_rows(eng, coords, k, lo, hi, chunk=32768):
     return out
 
 
-def run_ours(args):
+def measure(args, mode, rank, world, local, eng, with_cpu):
+    """One measurement of the hot path in `mode`:
+      "strong"  ONE hemisphere, centres in Morton order, rank r takes the r-th contiguous range (vertex-sharded,
+                north_star (5)); the score blocks are all-gathered once per step
+      "weak"    every rank runs one whole hemisphere job of its own (replicas; BASELINE configs[4] distributes whole
+                searchlights), no collective on the data path
+    Returns the pieces of the JSON line."""
     import torch
     import torch.distributed as dist
     from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
-    from multimodal_decoding_b200.sharding import spatial_order, split_bounds
+    from multimodal_decoding_b200.sharding import gather_scores, spatial_order, split_bounds
     from sklearn.linear_model import Ridge
 
-    rank, world, local = dist_setup(args)
-    torch.cuda.set_device(local)
     device = torch.device("cuda", local)
-    eng = sl.get_engine(local)
-    if args.batch_centres or args.cluster_size or args.group_size:
-        eng.configure(cluster_size=args.cluster_size, batch_centres=args.batch_centres, group_size=args.group_size)
     stream = torch.cuda.ExternalStream(eng.stream_ptr, device=device)
-    K, W, cps, k = args.steps, args.warmup, args.centres_per_step, args.n_neighbors
+    K, W, k = args.steps, args.warmup, args.n_neighbors
+    weak = mode == "weak" or world == 1
 
     t_setup = time.perf_counter()
-    weak = args.scaling == "weak" or world == 1
     coords, X16, Y16, ids = make_workload(args, device, seed=rank if weak else 0)
     V = len(coords)
     torch.cuda.synchronize()
@@ -334,8 +405,11 @@ def run_ours(args):
     A_all = A_all[order]
     lo, hi = (0, V) if weak else split_bounds(V, world)[rank]
     cps = hi - lo if args.centres_per_step == 0 else min(args.centres_per_step, hi - lo)
+    if not weak:                                                # every rank times the same number of centres
+        cps = min(cps, min(b - a for a, b in split_bounds(V, world)))
     n_rows = min(hi - lo, (W + K) * cps)
     A = A_all[lo:lo + n_rows]
+    del A_all
     is_cap = np.arange(140) < 70
     estimator = Ridge(alpha=1.0, fit_intercept=False)
 
@@ -371,8 +445,7 @@ def run_ours(args):
         t0 = time.perf_counter()
         for s in range(W, W + K):
             scores, flags = eng.searchlight(rows_of(s), 1.0)
-            if world > 1:
-                from multimodal_decoding_b200.sharding import gather_scores
+            if world > 1 and not weak:
                 gather_scores(scores, cps * world)           # the path's one collective: (V_shard x 8) blocks
         ev1.record(stream)
         barrier()
@@ -412,39 +485,89 @@ def run_ours(args):
                "api": "custom_search_light(X_host_f16, y_host_f16, Ridge(alpha=1), A_rows, ...)"}
     else:
         Xh, Yh = X16.cpu().numpy(), Y16.cpu().numpy()
+        del X16, Y16
 
-    cpu = None
-    if rank == 0 and not args.no_cpu_baseline:
-        # only the columns the sample touches travel to the worker processes
-        used = np.unique(A[:args.cpu_centres])
-        A_cpu = np.searchsorted(used, A[:args.cpu_centres])
-        v, n, dt, cores = cpu_centres_per_sec(np.ascontiguousarray(Xh[:, used]), Yh, A_cpu, ids, args.cpu_centres)
-        cpu = {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{n} consecutive centres of the same workload in {dt:.1f} s (float64 numpy/scipy oracle of "
-                         f"the reference loop, {cores} joblib processes over chunks of centres like "
-                         f"searchlight.py:130-148, one BLAS thread each)"}
+    cpu = parity = None
+    if rank == 0 and with_cpu:
+        n_cpu = min(args.cpu_centres, len(A))
+        if reference_available():
+            arm = RefArm(Xh, Yh, ids)
+            v, desc, ref_scores = reference_centres_per_sec(arm, A, n_cpu)
+            arm.close()
+            cpu = {"value": round(v, 3), "unit": UNIT, "cores": arm.cores, "kind": "reference", "sample": desc}
+            # parity of the same centres: GPU scores against the reference's
+            eng.upload(Xh, Yh, ids[0], ids[1], ids[2], is_cap)
+            eng.enable_margins(True)
+            got, fl = eng.searchlight(A[:len(ref_scores)], 1.0)
+            margins = eng.margins(len(ref_scores))
+            eng.enable_margins(False)
+            diff = np.abs(got - ref_scores)
+            parity = {"n": int(len(ref_scores)), "max_abs_diff": float(diff.max()),
+                      "n_centres_differing": int((diff.max(axis=1) > 0).sum()), "min_margin": float(margins.min()),
+                      "flags": int(fl.sum()), "against": "unmodified reference (baseline/_ref), same X, same centres"}
+        else:
+            # only the columns the sample touches travel to the worker processes
+            used = np.unique(A[:n_cpu])
+            A_cpu = np.searchsorted(used, A[:n_cpu])
+            v, n, dt, cores = cpu_centres_per_sec(np.ascontiguousarray(Xh[:, used]), Yh, A_cpu, ids, n_cpu)
+            cpu = {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": f"{n} consecutive centres of the same workload in {dt:.1f} s (baseline/_ref absent: float64 "
+                             f"numpy/scipy oracle of the reference loop, {cores} joblib processes over chunks of centres like "
+                             f"searchlight.py:130-148, one BLAS thread each)"}
+    del Xh, Yh
+    return {"value": value, "dev_s": dev_s, "wall": wall, "stats": stats, "e2e": e2e, "cpu": cpu, "parity": parity,
+            "clocks": clocks.summary(), "cps": cps, "V": V, "weak": weak, "n_rows": n_rows, "knn_s": knn_s,
+            "upload_s": upload_s, "upload_stats": upload_stats, "setup_s": setup_s}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+
+    rank, world, local = dist_setup(args)
+    torch.cuda.set_device(local)
+    eng = sl.get_engine(local)
+    if args.batch_centres or args.cluster_size or args.group_size:
+        eng.configure(cluster_size=args.cluster_size, batch_centres=args.batch_centres, group_size=args.group_size)
+    K, W, k = args.steps, args.warmup, args.n_neighbors
+    # N > 1: the headline is the north star's split -- ONE hemisphere, vertex-sharded ("strong"); the replica layout (one
+    # whole hemisphere job per GPU) is measured in the same run and reported beside it
+    mode = "weak" if world == 1 else args.scaling
+    m = measure(args, mode, rank, world, local, eng, with_cpu=not args.no_cpu_baseline)
+    replicas = None
+    if world > 1 and mode == "strong" and not args.no_replicas:
+        torch.cuda.empty_cache()
+        r = measure(args, "weak", rank, world, local, eng, with_cpu=False)
+        replicas = {"value": round(r["value"], 2), "unit": UNIT, "scaling": "weak",
+                    "ms_per_step": round(r["dev_s"] / K * 1e3, 3), "e2e": r["e2e"],
+                    "layout": f"{world} whole-hemisphere jobs, one per GPU, no data-path collective"}
     if rank == 0:
         peaks = load_peaks()
+        stats, cps, V, weak = m["stats"], m["cps"], m["V"], m["weak"]
         line = {
-            "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": round(dev_s / K * 1e3, 3), "higher_is_better": True,
-            "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "metric": METRIC, "value": round(m["value"], 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(m["dev_s"] / K * 1e3, 3), "higher_is_better": True,
+            "scaling": "weak" if (weak and world > 1) or args.scaling == "weak" else "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD,
                        "n_vertices": V, "n_neighbors": k, "n_train": args.n_train, "n_test": 140, "n_imagery": 3,
                        "n_dims": args.n_dims, "alpha": 1.0, "centres_per_step_per_gpu": cps,
-                       "sharding": (f"{world} hemisphere job(s), one per GPU, score maps all-gathered" if weak else
-                                    f"one hemisphere, Morton-ordered vertex ranges x{world}, score maps all-gathered"), "l2": "inputs larger than L2 (Xt 1.3 GB, per-step "
-                       "workspaces > 126 MB); no flush needed"},
-            "wall_ms_per_step": round(wall / K * 1e3, 3),
-            "e2e": e2e, "gpu_launches": int(stats["launches"]),
+                       "sharding": (f"{world} hemisphere job(s), one per GPU" if weak else
+                                    f"one hemisphere, Morton-ordered vertex ranges x{world}, score maps all-gathered"),
+                       "l2": "inputs larger than L2 (Xt 1.3 GB, per-step workspaces > 126 MB); no flush needed"},
+            "wall_ms_per_step": round(m["wall"] / K * 1e3, 3),
+            "e2e": m["e2e"], "gpu_launches": int(stats["launches"]),
             "roofline": roofline_entry(stats, cps * K, args, peaks),
-            "cpu_baseline": cpu, "clocks": clocks.summary(),
-            "setup": {"knn_rows": int(n_rows), "knn_s": round(knn_s, 2), "upload_s": round(upload_s, 3),
-                      "upload_stage_ms": {s: round(v, 2) for s, v in upload_stats["stage_ms"].items() if v > 0},
-                      "total_s": round(setup_s, 1)},
+            "cpu_baseline": m["cpu"], "parity_sample": m["parity"], "replicas": replicas, "clocks": m["clocks"],
+            "setup": {"knn_rows": int(m["n_rows"]), "knn_s": round(m["knn_s"], 2), "upload_s": round(m["upload_s"], 3),
+                      "upload_stage_ms": {s: round(v, 2) for s, v in m["upload_stats"]["stage_ms"].items() if v > 0},
+                      "total_s": round(m["setup_s"], 1)},
             "clusters_per_step": stats["clusters"] / K,
+            "rerouted_centres_per_step": stats["rerouted_centres"] / K,
             "host_ms_per_step": {"plan": round(stats["host_plan_ms"] / K, 1),
-                                 "adjacency_h2d": round(stats["host_adjacency_h2d_ms"] / K, 1)},
+                                 "adjacency_h2d": round(stats["host_adjacency_h2d_ms"] / K, 1),
+                                 "plan_cache_hits": int(stats["plan_cache_hits"])},
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -453,56 +576,61 @@ def run_ours(args):
 
 
 def run_reference(args):
-    """The reference's CPU path for the same workload: per-centre float64 ridge + scoring on the host cores."""
+    """The reference's own CPU implementation of the path on this box's host cores: the unmodified `custom_search_light`
+    (baseline/_ref) on a bounded sample of the own arm's workload -- same generator, same seed, full-width X; falls back
+    to the oracle port only when baseline/_ref is absent (and says so)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from multimodal_decoding_b200 import synthetic as syn
+    import torch
     k, n_tr, D = args.n_neighbors, args.n_train, args.n_dims
     cores = host_cores()
     n_c = 8 * cores                                             # centres per step (bounded sample)
-    mesh = syn.make_mesh(level=args.mesh_level, seed=7)
-    rng = np.random.default_rng(0)
-    # the neighbourhood columns of the sampled centres only: same shapes/dtypes as the GPU arm's workload
-    c64 = mesh.coords.astype(np.float64)
-    d0 = c64 - c64[0]                                           # a compact patch of cortex, like a GPU cluster
-    centres = np.argsort((d0[:, 0] ** 2 + d0[:, 1] ** 2) + d0[:, 2] ** 2, kind="stable")[:(args.warmup + args.steps) * n_c]
-    nbrs = []
-    for c in centres:
-        d = c64 - c64[c]
-        nbrs.append(np.argsort((d[:, 0] ** 2 + d[:, 1] ** 2) + d[:, 2] ** 2, kind="stable")[:k])
-    used = np.unique(np.concatenate(nbrs))
-    A = np.searchsorted(used, np.array(nbrs))
-    n_total = n_tr + 143
-    z = rng.standard_normal((n_total, 32))
-    X = (0.35 * z @ rng.standard_normal((32, len(used))) + rng.standard_normal((n_total, len(used))))
-    Y = z @ rng.standard_normal((32, D)) + 0.5 * rng.standard_normal((n_total, D))
-    X = ((X - X[:n_tr].mean(0)) / X[:n_tr].std(0)).astype(np.float16)
-    Y = ((Y - Y[:n_tr].mean(0)) / Y[:n_tr].std(0)).astype(np.float16)
-    ids = (np.arange(n_tr), np.arange(n_tr, n_tr + 140), np.arange(n_tr + 140, n_total))
-    arm = CpuArm(X, Y, A, ids)
-    step = lambda s: arm.step(range(s * n_c, (s + 1) * n_c))
+    n_rows = (args.warmup + args.steps) * n_c
+    device = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
+    coords, X16, Y16, ids = make_workload(args, device, seed=0)  # the own arm's generator and seed
+    Xh, Yh = X16.cpu().numpy(), Y16.cpu().numpy()
+    del X16, Y16
+    if device.type == "cuda":
+        torch.cuda.empty_cache()
+    from sklearn.neighbors import NearestNeighbors              # the k-NN branch of get_adjacency_matrix (searchlight.py:173)
+    n_rows = min(n_rows, len(coords))
+    A = NearestNeighbors().fit(coords).kneighbors(coords[:n_rows], n_neighbors=k, return_distance=False)
+    use_ref = reference_available()
+    if use_ref:
+        arm = RefArm(Xh, Yh, ids)
+        step = lambda s: arm.run(A[s * n_c:(s + 1) * n_c], cores)
+        kind = "reference"
+        how = (f"unmodified custom_search_light + sklearn Ridge(alpha=1) from baseline/_ref, n_jobs={cores} "
+               f"(searchlight.py:130-148), full-width X ({arm.versions}, BLAS {arm.blas})")
+    else:
+        used = np.unique(A)
+        arm = CpuArm(np.ascontiguousarray(Xh[:, used]), Yh, np.searchsorted(used, A), ids)
+        step = lambda s: arm.step(range(s * n_c, (s + 1) * n_c))
+        kind = "port"
+        how = (f"baseline/_ref absent: float64 numpy/scipy oracle of the reference loop, {cores} joblib processes over chunks "
+               f"of centres, one BLAS thread each")
+    n_steps_avail = max(n_rows // n_c, 1)
     for s in range(max(args.warmup, 1)):
-        step(s % (args.warmup + args.steps))
+        step(s % n_steps_avail)
     t0 = time.perf_counter()
     for s in range(args.warmup, args.warmup + args.steps):
-        step(s)
+        step(s % n_steps_avail)
     dt = time.perf_counter() - t0
     arm.close()
     v = n_c * args.steps / dt
-    sample = (f"{n_c} centres per step x {args.steps} steps, k={k}, N_train={n_tr}, D={D}; {cores} joblib processes "
-              f"over chunks of centres (searchlight.py:130-148), one BLAS thread each")
+    sample = f"{n_c} consecutive centres per step x {args.steps} steps, k={k}, N_train={n_tr}, D={D}; {how}"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 2),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         # the own arm's workload; each step is a bounded sample of its centres (cpu_baseline.sample)
-        "config": {"workload": WORKLOAD, "n_vertices": int(len(mesh.coords)), "n_neighbors": k, "n_train": n_tr,
-                   "n_test": 140, "n_imagery": 3, "n_dims": D, "alpha": 1.0, "centres_per_step": n_c},
-        "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": WORKLOAD, "n_vertices": int(len(coords)), "n_neighbors": k, "n_train": n_tr,
+                   "n_test": 140, "n_imagery": 3, "n_dims": D, "alpha": 1.0, "centres_per_step_sampled": n_c},
+        "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "CPU restatement of the reference loop (the reference is Python + sklearn/scipy and cannot travel "
-                "to the GPU box); float64, all host cores"}), flush=True)
+        "note": "the reference's CPU path (Python + sklearn/scipy, float64) on all host cores; inputs generated like the own "
+                "arm's (same seed)"}), flush=True)
 
 
 if __name__ == "__main__":

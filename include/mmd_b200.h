@@ -81,10 +81,23 @@ int mmd_radius_neighbors(mmd_handle* h, const double* coords, int n_vertices, do
  *   test_is_caption[n_test]             1 where TEST_STIM_TYPES == "caption" (data.py:182-187), else 0
  * Builds the vertex-major panels and X_train^T Y_train once (used by every centre).  Returns once X and Y have been
  * read; the kernels stay in flight on the handle's stream.  NaN / infinity in X or in the training rows of Y is
- * recorded here and reported by the searchlight calls (below). */
+ * recorded here and reported by the searchlight calls (below).
+ * Ordering contract for DEVICE pointers: X / Y are read by kernels on the handle's own non-blocking stream (mmd_stream),
+ * which is not ordered behind any other stream.  The caller must make sure the work that produced them has completed
+ * (stream or event synchronisation) before calling; the Python Engine synchronises torch's current stream for tensors. */
 int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
                const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
                const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery);
+
+/* mmd_upload for a rank that scores only part of the surface (vertex-sharded searchlight, north_star (5); the reference's
+ * joblib chunks of searchlight.py:130-148): `active_vertices` (n_active ascending vertex ids, HOST; NULL / 0 = all) lists
+ * the vertices the rank's neighbourhoods use.  X^T Y rows and the digit planes of the integer prediction GEMM are built
+ * for those vertices only (the per-upload work shrinks with the shard); a later searchlight call whose neighbourhoods
+ * leave the set fails with a message naming mmd_upload_active. */
+int mmd_upload_active(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
+                      const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
+                      const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery,
+                      const int32_t* active_vertices, int n_active);
 
 /* Replaces the loop of custom_group_iter_search_light + train_and_test (searchlight.py:38-114) for
  * `n_centres` centres with a fixed neighbourhood size k: ridge fit with `alpha`
@@ -190,9 +203,11 @@ const char* mmd_stage_name(int i);
  * [1] shared-core factorisations, [2] centres that used a shared core, [3] sum of their shared prefix lengths,
  * [4] host microseconds spent grouping centres (clusters, unions, shared cores), [5] host microseconds to hand the
  * adjacency to the device, [6] centres whose predictions were redone by the float64 kernels because a comparison sat
- * inside the error bound of the integer prediction GEMM (mmd_set_predict_mode);
+ * inside the error bound of the integer prediction GEMM (mmd_set_predict_mode), [7] searchlight calls that reused the
+ * host plan of the previous call (same adjacency: clusters, unions and shared cores are kept, the adjacency is not copied
+ * to the device again);
  * solve_flops = float64 flops executed by the factorisation / triangular-solve stage. */
-#define MMD_N_COUNTERS 7
+#define MMD_N_COUNTERS 8
 int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* solve_flops);
 
 /* Prefix sharing: up to `group_size` neighbouring centres factor the part of their normal matrices that belongs to

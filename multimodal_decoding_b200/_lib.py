@@ -8,12 +8,12 @@ LIB_PATH = os.environ.get("MMD_B200_LIB") or os.path.join(_HERE, "libmmd_b200.so
 
 N_SCORES = 8
 N_STAGES = 10
-N_COUNTERS = 7
+N_COUNTERS = 8
 N_NULL_SCORES = 6
 EVAL_PAD = 144
 
 EXPORTS = [
-    "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload",
+    "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload", "mmd_upload_active",
     "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_searchlight_cv", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
     "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels", "mmd_check_guards", "mmd_guard_selftest",
@@ -57,6 +57,8 @@ def load():
     lib.mmd_radius_neighbors.restype = i32
     lib.mmd_upload.argtypes = [vp, vp, i32, i32, vp, i32, vp, i32, vp, i32, vp, vp, i32]
     lib.mmd_upload.restype = i32
+    lib.mmd_upload_active.argtypes = [vp, vp, i32, i32, vp, i32, vp, i32, vp, i32, vp, vp, i32, vp, i32]
+    lib.mmd_upload_active.restype = i32
     lib.mmd_searchlight.argtypes = [vp, vp, i32, i32, dbl, vp, vp]
     lib.mmd_searchlight.restype = i32
     lib.mmd_searchlight_i64.argtypes = [vp, vp, i32, i32, dbl, vp, vp]

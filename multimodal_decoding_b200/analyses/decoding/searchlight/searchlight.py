@@ -176,8 +176,20 @@ def _require_rectangular(A, what):
     return A
 
 
+def _active_vertices(A, n_vertices):
+    """Ascending ids of the vertices the neighbourhoods in `A` use; None when that is (nearly) all of them."""
+    mask = np.zeros(n_vertices, dtype=bool)
+    if _is_ragged(A):
+        for r in A:
+            mask[np.asarray(r)] = True
+    else:
+        mask[np.asarray(A).ravel()] = True
+    active = np.flatnonzero(mask)
+    return None if len(active) > 0.9 * n_vertices else active
+
+
 def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *, device=None, is_caption=None,
-                        upload=True, anchors=None):
+                        upload=True, anchors=None, shard_only=False):
     """(n_centres x 8) float64 score block and per-centre flags for the centres in `A` on one GPU.
     `anchors` (ragged `A` only): the vertex each centre sits on, used to group nearby centres."""
     eng = get_engine(device)
@@ -187,7 +199,9 @@ def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *,
     if upload:
         if is_caption is None:
             is_caption = _is_caption_mask(len(test_ids))
-        eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption)
+        # a rank of a vertex-sharded call stages the cross-covariance rows of its own neighbourhoods only
+        active = _active_vertices(A, np.shape(X)[1]) if shard_only and len(A) else None
+        eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption, active_vertices=active)
     if grid:
         return search_light_cv(eng, A, grid[0], grid[1], len(train_ids))[:2]
     if _is_ragged(A):
@@ -247,7 +261,7 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
         # radius mode: centre i sits on vertex i (searchlight.py:143-148 enumerates the rows of A by vertex)
         anchors = np.arange(lo, hi) if _is_ragged(A) and len(A) == np.shape(X)[1] else None
         scores, flags = search_light_scores(X, y, estimator, A[lo:hi], train_ids, test_ids, imagery_ids,
-                                            anchors=anchors)
+                                            anchors=anchors, shard_only=(hi - lo) < len(A))
     else:
         _require_rectangular(A, "the null-distribution branch")
         eng = get_engine()

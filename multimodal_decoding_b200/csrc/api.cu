@@ -162,7 +162,9 @@ struct mmd_handle {
     DevBuf adj, union_vertices, task_row, task_k, task_core_off, task_core_n, core_work, group_flags, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
-    DevBuf vertex_bad, y_bad;               // per vertex: betas hold NaN/inf; one int: training latents hold NaN/inf
+    DevBuf vertex_bad, y_bad;               // per vertex: 1 = betas hold NaN/inf, 2 = outside the active set; one int: training latents hold NaN/inf
+    DevBuf active;                          // mmd_upload_active: the vertices whose XtY rows / digit planes exist
+    int n_active = 0;                       // 0 = all vertices
     DevBuf up_x, up_y, up_train, up_eval;   // mmd_upload's staging copies: alive until the packing kernels have run
     cudaEvent_t up_copied = nullptr;        // recorded behind the last host-to-device copy of mmd_upload
     PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
@@ -172,6 +174,8 @@ struct mmd_handle {
     // their scales, the score kernel's tolerance input, the list of centres handed back to the float64 kernels
     DevBuf xplanes, sX, colmax, zplanes, sZ, amp2, i8_status, reroute_list, reroute_counts, margins;
     CvState* cv = nullptr;          // non-null while mmd_searchlight_cv runs
+    struct PlanCache* plan_cache = nullptr;     // clusters / unions / groups of the last adjacency (run_searchlight)
+    int64_t plan_hits = 0;
     int predict_mode = 1;           // 1: tcgen05 int8 digit GEMM + float64 reroute of guarded centres; 0: float64 DMMA kernel
     int n_sms = 148;
     int call_batches = 0;           // batches of the current searchlight call (index into reroute_counts)
@@ -292,6 +296,22 @@ struct Clustering {
     std::vector<int> centre_of;   // vertex -> the centre sitting on it (-1: none)
     std::vector<int> cl_off, members;
 };
+
+}  // namespace
+// The host plan depends only on the adjacency (and the grouping knobs): the same adjacency serves every training mode and
+// feature model of a subject-hemisphere (searchlight.py:186-236 loops over them), so the plan of the last adjacency is kept
+// and reused when a call presents the same one (two independent 64-bit hashes over the staged int32 copy + its shape).
+struct PlanCache {
+    bool valid = false;
+    uint64_t h1 = 0, h2 = 0;
+    long total = 0;
+    int n = 0, k = 0, V = 0, cluster_size = 0, group_size = 0, batch_cap = 0, ragged = 0;
+    bool adj_on_device = false;
+    Clustering cl;
+    std::vector<int> chunk_start;
+    std::vector<Plan> plans;
+};
+namespace {
 
 void cluster_centres(const Rows& rows, int V, int cluster_size, Clustering& cl) {
     // greedy region growing: a seed takes its nearest still-unassigned centres (k-NN adjacency rows are ordered
@@ -484,8 +504,9 @@ int run_xty(mmd_handle* h) {
     GemmProblem p{};
     p.A = h->Xt.as<__half>();
     p.lda = h->ldt;
-    p.rowsA = nullptr;
-    p.M = h->V;
+    p.rowsA = h->n_active ? h->active.as<int>() : nullptr;      // a vertex subset: rows land at their vertex index
+    p.scatter_c = h->n_active ? 1 : 0;
+    p.M = h->n_active ? h->n_active : h->V;
     p.B = h->Yt.as<__half>();
     p.ldb = h->ldt;
     p.rowsB = nullptr;
@@ -505,7 +526,8 @@ int run_xty(mmd_handle* h) {
         CU(h->colmax.ensure((size_t)h->Dp * sizeof(unsigned long long)));
         span_begin(h, ST_XTY);
         CU(launch_slice_xty(h->XtY.as<double>(), h->V, h->Dp, h->xplanes.as<int8_t>(), h->sX.as<double>(),
-                            h->colmax.as<unsigned long long>(), h->stream));
+                            h->colmax.as<unsigned long long>(), h->n_active ? h->active.as<int>() : nullptr, h->n_active,
+                            h->stream));
         span_end(h, 3);
     }
     return 0;
@@ -925,10 +947,12 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     const auto t_stage0 = std::chrono::steady_clock::now();
     const size_t total = (size_t)rows_in.total();
     CU(h->adj_host.ensure(std::max<size_t>(total, 1) * sizeof(int32_t)));
+    uint64_t hash1 = 0xcbf29ce484222325ull, hash2 = 0x84222325cbf29ce4ull;
     {
         int32_t* dst = reinterpret_cast<int32_t*>(h->adj_host.p);
         const int32_t* src32 = rows_in.data;
         const int nt = (int)std::max<size_t>(1, std::min<size_t>(n_threads, total / (1 << 20) + 1));
+        std::vector<uint64_t> part1(nt), part2(nt);
         auto conv = [&](int t) {
             const size_t lo = total * t / nt, hi = total * (t + 1) / nt;
             if (data64) {
@@ -939,18 +963,35 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
             } else {
                 memcpy(dst + lo, src32 + lo, (hi - lo) * sizeof(int32_t));
             }
+            uint64_t a = 0x9e3779b97f4a7c15ull ^ lo, b = 0xc2b2ae3d27d4eb4full + lo;
+            for (size_t i = lo; i < hi; ++i) {
+                const uint64_t v = (uint32_t)dst[i];
+                a = (a ^ v) * 0x100000001b3ull;
+                b = (b + v) * 0xff51afd7ed558ccdull;
+                b ^= b >> 29;
+            }
+            part1[t] = a;
+            part2[t] = b;
         };
         std::vector<std::thread> pool;
         for (int t = 1; t < nt; ++t) pool.emplace_back(conv, t);
         conv(0);
         for (auto& t : pool) t.join();
+        for (int t = 0; t < nt; ++t) {
+            hash1 = (hash1 ^ part1[t]) * 0x100000001b3ull;
+            hash2 = (hash2 + part2[t]) * 0xff51afd7ed558ccdull;
+        }
+        hash1 ^= (uint64_t)nt << 56;                       // the segmentation is part of the value
+        if (rows_in.off)
+            for (int i = 0; i <= n_centres; ++i) hash2 = (hash2 ^ (uint64_t)rows_in.off[i]) * 0x100000001b3ull;
+        if (rows_in.anchors)
+            for (int i = 0; i < n_centres; ++i) hash1 = (hash1 + (uint32_t)rows_in.anchors[i]) * 0xff51afd7ed558ccdull;
     }
     Rows rows = rows_in;
     rows.data = reinterpret_cast<const int32_t*>(h->adj_host.p);
     // adjacency rows, then (after grouping) the shared cores: at most half as many entries again
+    const void* adj_before = h->adj.p;
     CU(h->adj.ensure((total + total / 2 + 2) * sizeof(int)));
-    CU(cudaMemcpyAsync(h->adj.p, rows.data, total * sizeof(int), cudaMemcpyHostToDevice, h->stream));
-    h->adj_h2d_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_stage0).count();
     const int kp = round_up(k_max, NB);
 
     // Centres per batch: the configured size, capped so that the per-centre workspaces (factor + solve panel, shared
@@ -988,28 +1029,54 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     if (h->want_margins) CU(h->margins.ensure((size_t)n_centres * sizeof(double)));
 
     // Clusters for the whole call, then plans for ranges of clusters ("chunks" of two or more batches): the plan of chunk
-    // i+1 is built by host threads while the GPU executes chunk i.
+    // i+1 is built by host threads while the GPU executes chunk i.  The plan of the last adjacency is kept (PlanCache).
+    if (!h->plan_cache) h->plan_cache = new PlanCache();
+    PlanCache& pc = *h->plan_cache;
+    const bool hit = pc.valid && pc.h1 == hash1 && pc.h2 == hash2 && pc.total == (long)total && pc.n == n_centres &&
+                     pc.k == k_max && pc.V == h->V && pc.cluster_size == h->cluster_size && pc.group_size == h->group_size &&
+                     pc.batch_cap == batch_cap && pc.ragged == (rows.off ? 1 : 0);
+    if (!(hit && pc.adj_on_device && adj_before == h->adj.p))
+        CU(cudaMemcpyAsync(h->adj.p, rows.data, total * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    h->adj_h2d_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_stage0).count();
     auto t_host0 = std::chrono::steady_clock::now();
-    Clustering cl;
-    cluster_centres(rows, h->V, h->cluster_size, cl);
+    pc.valid = false;                                          // set again when the call has gone through
+    pc.adj_on_device = false;
+    if (hit) {
+        ++h->plan_hits;
+    } else {
+        pc.h1 = hash1;
+        pc.h2 = hash2;
+        pc.total = (long)total;
+        pc.n = n_centres;
+        pc.k = k_max;
+        pc.V = h->V;
+        pc.cluster_size = h->cluster_size;
+        pc.group_size = h->group_size;
+        pc.batch_cap = batch_cap;
+        pc.ragged = rows.off ? 1 : 0;
+        cluster_centres(rows, h->V, h->cluster_size, pc.cl);
+        const int n_cl = (int)pc.cl.cl_off.size() - 1;
+        pc.chunk_start.assign(1, 0);
+        const int chunk_target = std::max(2 * batch_cap, 12288);      // centres per chunk: whole batches, never more
+        for (int c = 0, acc = 0; c < n_cl; ++c) {
+            const int m = pc.cl.cl_off[c + 1] - pc.cl.cl_off[c];
+            if (acc > 0 && acc + m > chunk_target) {
+                pc.chunk_start.push_back(c);
+                acc = 0;
+            }
+            acc += m;
+        }
+        pc.chunk_start.push_back(n_cl);
+        pc.plans.assign(pc.chunk_start.size() - 1, Plan());
+    }
+    const Clustering& cl = pc.cl;
+    const std::vector<int>& chunk_start = pc.chunk_start;
     const int n_clusters = (int)cl.cl_off.size() - 1;
     h->n_clusters += n_clusters;
-    std::vector<int> chunk_start(1, 0);
-    const int chunk_target = std::max(2 * batch_cap, 12288);      // centres per chunk: whole batches, never more
-    for (int c = 0, acc = 0; c < n_clusters; ++c) {
-        const int m = cl.cl_off[c + 1] - cl.cl_off[c];
-        if (acc > 0 && acc + m > chunk_target) {
-            chunk_start.push_back(c);
-            acc = 0;
-        }
-        acc += m;
-    }
-    chunk_start.push_back(n_clusters);
     const int n_chunks = (int)chunk_start.size() - 1;
-    Plan plans[2];
     const int group_size = h->group_size, V = h->V;
-    auto plan_chunk = [&, group_size, V, n_threads](int i) {
-        build_plan(rows, V, cl, chunk_start[i], chunk_start[i + 1], group_size, n_threads, plans[i & 1]);
+    auto plan_chunk = [&, group_size, V, n_threads, hit](int i) {
+        if (!hit) build_plan(rows, V, cl, chunk_start[i], chunk_start[i + 1], group_size, n_threads, pc.plans[i]);
     };
     std::future<void> pending = std::async(std::launch::async, plan_chunk, 0);
     int rc = 0;
@@ -1017,9 +1084,10 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
         pending.get();                                     // exposed host time: only what the GPU did not hide
         h->plan_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t_host0).count();
         if (i + 1 < n_chunks) pending = std::async(std::launch::async, plan_chunk, i + 1);
-        rc = run_chunk(h, rows, plans[i & 1], total, k_max, kp, alpha, with_null, raw_yhat, batch_cap);
+        rc = run_chunk(h, rows, pc.plans[i], total, k_max, kp, alpha, with_null, raw_yhat, batch_cap);
         t_host0 = std::chrono::steady_clock::now();
     }
+    if (rc == 0) pc.valid = pc.adj_on_device = true;
     if (pending.valid()) pending.wait();                   // an error path must not leave the planner running
     return rc;
 }
@@ -1029,6 +1097,7 @@ int report_input_flags(mmd_handle* h, int bad, int y_bad, const char* who) {
     if (bad & 2) return fail(h, "%s: adjacency holds a vertex index outside [0, %d)", who, h->V);
     // sklearn's Ridge.fit / predict validate their inputs (check_array) and raise ValueError
     if (bad & 4) return fail(h, "Input X contains NaN or infinity (%s: a neighbourhood uses a vertex whose betas are not finite)", who);
+    if (bad & 8) return fail(h, "%s: a neighbourhood uses a vertex outside the active set given to mmd_upload_active", who);
     if (y_bad) return fail(h, "Input y contains NaN or infinity (%s: training latents must be finite)", who);
     if (bad & 1) return fail(h, "internal: neighbour missing from its cluster union");
     return 0;
@@ -1042,7 +1111,7 @@ std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
                       &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval,
                       &h->xplanes, &h->sX, &h->colmax, &h->zplanes, &h->sZ, &h->amp2, &h->i8_status, &h->reroute_list,
-                      &h->reroute_counts, &h->margins};
+                      &h->reroute_counts, &h->margins, &h->active};
 }
 
 // the stream must have passed mmd_upload's kernels (any later synchronisation of h->stream will do)
@@ -1127,6 +1196,7 @@ void mmd_destroy(mmd_handle* h) {
     release_upload_staging(h);
     if (h->up_copied) cudaEventDestroy(h->up_copied);
     h->adj_host.release();
+    delete h->plan_cache;
     for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream);
     delete h;
@@ -1187,7 +1257,7 @@ void mmd_reset_stats(mmd_handle* h) {
     h->n_clusters = 0;
     h->syrk_flops = 0.0;
     h->solve_flops = 0.0;
-    h->n_batches = h->n_core_tasks = h->n_grouped = h->sum_sp = h->plan_us = h->adj_h2d_us = h->n_rerouted = 0;
+    h->n_batches = h->n_core_tasks = h->n_grouped = h->sum_sp = h->plan_us = h->adj_h2d_us = h->n_rerouted = h->plan_hits = 0;
 }
 
 int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* solve_flops) {
@@ -1200,6 +1270,7 @@ int mmd_get_counters(mmd_handle* h, int64_t counters[MMD_N_COUNTERS], double* so
         counters[4] = h->plan_us;
         counters[5] = h->adj_h2d_us;
         counters[6] = h->n_rerouted;
+        counters[7] = h->plan_hits;
     }
     if (solve_flops) *solve_flops = h->solve_flops;
     return 0;
@@ -1350,7 +1421,20 @@ int mmd_radius_neighbors(mmd_handle* h, const double* coords, int n_vertices, do
 int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
                const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
                const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery) {
+    return mmd_upload_active(h, X, n_total, n_vertices, Y, n_dims, train_ids, n_train, test_ids, n_test, test_is_caption,
+                             imagery_ids, n_imagery, nullptr, 0);
+}
+
+int mmd_upload_active(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
+                      const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
+                      const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery,
+                      const int32_t* active_vertices, int n_active) {
     if (!h) return 1;
+    if (n_active < 0 || (n_active > 0 && !active_vertices)) return fail(h, "mmd_upload_active: bad active-vertex list");
+    for (int i = 0; i < n_active; ++i)
+        if (active_vertices[i] < 0 || active_vertices[i] >= n_vertices || (i > 0 && active_vertices[i] <= active_vertices[i - 1]))
+            return fail(h, "mmd_upload_active: active vertices must be ascending indices in [0, %d)", n_vertices);
+    if (n_active == n_vertices) n_active = 0;
     if (!X || !Y || !train_ids || (n_test > 0 && (!test_ids || !test_is_caption)) || (n_imagery > 0 && !imagery_ids))
         return fail(h, "mmd_upload: null pointer");
     if (n_total < 1 || n_vertices < 1 || n_dims < 1 || n_train < 1) return fail(h, "mmd_upload: empty input");
@@ -1420,7 +1504,14 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
         CUB(cudaMemsetAsync(h->Yt.p, 0, (size_t)h->Dp * h->ldt * sizeof(__half), h->stream));
         CUB(h->vertex_bad.ensure((size_t)n_vertices));
         CUB(h->y_bad.ensure(sizeof(int)));
-        CUB(cudaMemsetAsync(h->vertex_bad.p, 0, (size_t)n_vertices, h->stream));
+        h->n_active = n_active;
+        if (n_active) {
+            if ((rc = to_device(h, h->active, active_vertices, n_active))) break;
+            CUB(cudaMemsetAsync(h->vertex_bad.p, 2, (size_t)n_vertices, h->stream));
+            CUB(launch_clear_bytes(h->vertex_bad.as<unsigned char>(), h->active.as<int>(), n_active, h->stream));
+        } else {
+            CUB(cudaMemsetAsync(h->vertex_bad.p, 0, (size_t)n_vertices, h->stream));
+        }
         CUB(cudaMemsetAsync(h->y_bad.p, 0, sizeof(int), h->stream));
         span_begin(h, ST_PACK);
         launch_pack_transpose(Xd, n_vertices, d_train.as<int>(), n_train, n_vertices, h->Xt.as<__half>(), h->ldt,

@@ -220,4 +220,13 @@ cudaError_t launch_fold_latents(const __half* Yt, long ldy, int col0, int n_rows
     return cudaGetLastError();
 }
 
+// flags[idx[i]] = 0
+__global__ void clear_bytes_kernel(unsigned char* __restrict__ flags, const int* __restrict__ idx, int n) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) flags[idx[i]] = 0;
+}
+cudaError_t launch_clear_bytes(unsigned char* flags, const int* idx, int n, cudaStream_t s) {
+    clear_bytes_kernel<<<148, 256, 0, s>>>(flags, idx, n);
+    return cudaGetLastError();
+}
+
 }  // namespace mmd

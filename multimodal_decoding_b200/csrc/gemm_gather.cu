@@ -103,7 +103,8 @@ __global__ void __launch_bounds__(256, 2) gemm_nt_f16_f64_kernel(const GemmProbl
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             int col = n0 + wn * 32 + j * 8 + 2 * fk;
-            double* c = p.C + (long)row * p.ldc + col;
+            const long crow_out = p.scatter_c && p.rowsA ? p.rowsA[row] : row;
+            double* c = p.C + crow_out * p.ldc + col;
             if (col + 1 < p.N) {
                 *reinterpret_cast<double2*>(c) = make_double2(acc[i][j][0], acc[i][j][1]);
             } else if (col < p.N) {

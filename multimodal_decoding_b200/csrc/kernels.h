@@ -27,6 +27,7 @@ struct GemmProblem {
     double* C;
     long ldc;           // even
     int lower_only;     // skip tiles strictly above the diagonal (symmetric rank-k update)
+    int scatter_c;      // 1: row i of the product is written to C row rowsA[i] (a row subset of a full-size result)
 };
 size_t gemm_gather_smem_bytes();
 cudaError_t launch_gemm_gather(const GemmProblem* probs_dev, int n_problems, int max_m, int max_n, cudaStream_t s);
@@ -111,8 +112,9 @@ struct PredictI8Params {
 };
 size_t predict_i8_smem_bytes();
 // planes: (I8_DIGITS x V x Dp) int8, sX: (Dp), colmax_ws: (Dp) scratch
+// rows (optional, device): only these n_rows rows of XtY exist (mmd_upload_active); maxima and planes cover them alone
 cudaError_t launch_slice_xty(const double* XtY, int V, int Dp, int8_t* planes, double* sX, unsigned long long* colmax_ws,
-                             cudaStream_t s);
+                             const int* rows, int n_rows, cudaStream_t s);
 // zplanes: (n_tasks x I8_DIGITS x EVAL_PAD x kp_max) int8, sZ: (n_tasks x EVAL_PAD); Zt is read from `work` as in PredictParams
 cudaError_t launch_slice_zt(const CentreTask* tasks, int n_tasks, int kp_max, const double* work, int8_t* zplanes, double* sZ,
                             cudaStream_t s);
@@ -184,6 +186,7 @@ size_t cv_score_smem_bytes();
 cudaError_t launch_cv_score(const CvScoreParams& p, cudaStream_t s);
 cudaError_t launch_copy_cols_f16(const __half* src, long ld_src, int col0, int n_cols, __half* dst, int ld_dst, long n_rows,
                                  cudaStream_t s);
+cudaError_t launch_clear_bytes(unsigned char* flags, const int* idx, int n, cudaStream_t s);
 cudaError_t launch_rsub(const double* a, double* inout, long n, cudaStream_t s);
 cudaError_t launch_fold_latents(const __half* Yt, long ldy, int col0, int n_rows, int n_rows_pad, int Dp, double* cand, double* sq,
                                 cudaStream_t s);

@@ -12,11 +12,12 @@
 // and a centre with a comparison inside its tolerance is redone by the float64 kernels (predict.cu), see score.cu.
 //
 // One persistent CTA per SM walks (centre, 128-feature tile) items:
-//   warp 0      TMA producer: the neighbour rows of the XtY digit planes arrive by cp.async.bulk.tensor ... tile::gather4
-//               (4 rows x 128 B per instruction, 128B-swizzled, MN-major operand A), the Zt digit planes by tiled TMA
-//               (144 x 64 B boxes, 64B-swizzled, K-major operand B); ring of 4 slots of 3 + 3 planes x 64 neighbours
-//   warp 1      one lane issues tcgen05.mma (M = 128 features, N = 144 evaluation rows, K = 32 per instruction) and
-//               commits the slots back to the producer
+//   warps 0,2,3 TMA producers, one digit plane of a ring slot each: the neighbour rows of the XtY digit planes arrive by
+//               cp.async.bulk.tensor ... tile::gather4 (4 rows x 128 B per instruction, 128B-swizzled, MN-major operand
+//               A), the Zt digit planes by tiled TMA (144 x 64 B boxes, 64B-swizzled, K-major operand B); ring of 4
+//               slots of 3 + 3 planes x 64 neighbours
+//   warp 1      issues tcgen05.mma (M = 128 features, N = 144 evaluation rows, K = 32 per instruction; the warp stays
+//               converged and one elected lane issues, descriptors in uniform registers) and commits the slots back
 //   warps 4-15  epilogue: tcgen05.ld, float64 recombination, per-feature z-scoring of the three prediction groups
 //               (StandardScaler semantics, as predict.cu), stores
 // TMEM holds three 144-column accumulators, so a tile takes two passes over its neighbours: weights 5,4,3 (all six
@@ -42,7 +43,7 @@ constexpr int ACC_STRIDE = 160;                  // accumulator of weight w live
 constexpr int TMEM_COLS = 512;
 constexpr int N_EPI_WARPS = 12, EPI_COLS = TN / 3;     // 3 column groups x 4 lane quarters
 constexpr int EPI_THREADS = N_EPI_WARPS * 32;
-constexpr int THREADS = 128 + EPI_THREADS;     // warps 0-3: producer, MMA issuer, two idle (one warpgroup); warps 4-15: epilogue
+constexpr int THREADS = 128 + EPI_THREADS;     // warps 0-3: three producers + the MMA issuer (one warpgroup); warps 4-15: epilogue
 constexpr int MAX_KP = 2048;
 static_assert(S == 6, "pass structure below is written for six digits");
 static_assert(SLOT_BYTES % 1024 == 0 && A_PLANE % 1024 == 0 && B_PLANE % 512 == 0, "swizzle atoms must stay aligned");
@@ -102,18 +103,28 @@ __device__ __forceinline__ uint64_t desc_b_k_sw64(uint32_t addr) {     // K-majo
     return ((uint64_t)hi << 32) | lo;
 }
 
+// Both are called by ALL lanes of the (converged) issuing warp with warp-uniform arguments; one elected lane issues.
+// Keeping the control flow convergent lets ptxas hold the descriptors in uniform registers instead of wrapping every
+// instruction in a per-lane broadcast loop.
 __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t"
-        ".reg .pred p;\n\t"
+        ".reg .pred p, e;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t"
         "}\n" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    asm volatile(
+        "{\n\t"
+        ".reg .pred e;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+        "}\n" ::"r"(bar)
+        : "memory");
 }
 
 __device__ __forceinline__ void tma_gather4(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int col, int r0, int r1, int r2, int r3) {
@@ -132,6 +143,7 @@ __device__ __forceinline__ void tma_tile2d(uint32_t dst, const CUtensorMap* tm, 
 }
 
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory"); }
+__device__ __forceinline__ void prod_barrier() { asm volatile("bar.sync 2, 96;" ::: "memory"); }
 
 }  // namespace
 
@@ -160,11 +172,12 @@ __device__ __forceinline__ double pow2_ceil(double amax) {
 }
 
 // column maxima of |A| (n_rows x n_cols, row-major) -> bits of the maximum per column (non-negative doubles order like integers)
-__global__ void colmax_kernel(const double* __restrict__ A, long n_rows, int n_cols, unsigned long long* __restrict__ colmax) {
+__global__ void colmax_kernel(const double* __restrict__ A, const int* __restrict__ rows, long n_rows, int n_cols,
+                              unsigned long long* __restrict__ colmax) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_cols) return;
     double m = 0.0;
-    for (long r = blockIdx.y; r < n_rows; r += gridDim.y) m = fmax(m, fabs(A[r * n_cols + c]));
+    for (long r = blockIdx.y; r < n_rows; r += gridDim.y) m = fmax(m, fabs(A[(rows ? (long)rows[r] : r) * n_cols + c]));
     atomicMax(colmax + c, (unsigned long long)__double_as_longlong(m));
 }
 __global__ void colscale_kernel(const unsigned long long* __restrict__ colmax, int n_cols, double* __restrict__ scale) {
@@ -172,12 +185,12 @@ __global__ void colscale_kernel(const unsigned long long* __restrict__ colmax, i
     if (c < n_cols) scale[c] = pow2_ceil(__longlong_as_double((long long)colmax[c]));
 }
 // planes[t][r][c] = digit t of A[r][c] / scale[c]; one thread cuts 16 consecutive columns of a row
-__global__ void slice_columns_kernel(const double* __restrict__ A, long n_rows, int n_cols, const double* __restrict__ scale,
-                                     int8_t* __restrict__ planes) {
+__global__ void slice_columns_kernel(const double* __restrict__ A, const int* __restrict__ rows, long n_list, long n_rows,
+                                     int n_cols, const double* __restrict__ scale, int8_t* __restrict__ planes) {
     const long chunks_per_row = n_cols / 16;
-    const long total = n_rows * chunks_per_row;
+    const long total = n_list * chunks_per_row;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        const long r = i / chunks_per_row;
+        const long r = rows ? (long)rows[i / chunks_per_row] : i / chunks_per_row;
         const int c0 = (int)(i % chunks_per_row) * 16;
         union { int8_t b[16]; int4 v; } out[S];
 #pragma unroll
@@ -198,14 +211,15 @@ __global__ void slice_columns_kernel(const double* __restrict__ A, long n_rows, 
 }
 
 cudaError_t launch_slice_xty(const double* XtY, int V, int Dp, int8_t* planes, double* sX, unsigned long long* colmax_ws,
-                             cudaStream_t s) {
+                             const int* rows, int n_rows, cudaStream_t s) {
     if (Dp % 16 != 0) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(colmax_ws, 0, (size_t)Dp * sizeof(unsigned long long), s);
     if (e != cudaSuccess) return e;
     dim3 g((Dp + 255) / 256, 592);
-    colmax_kernel<<<g, 256, 0, s>>>(XtY, V, Dp, colmax_ws);
+    const long n_list = rows ? n_rows : V;
+    colmax_kernel<<<g, 256, 0, s>>>(XtY, rows, n_list, Dp, colmax_ws);
     colscale_kernel<<<(Dp + 255) / 256, 256, 0, s>>>(colmax_ws, Dp, sX);
-    slice_columns_kernel<<<148 * 16, 256, 0, s>>>(XtY, V, Dp, sX, planes);
+    slice_columns_kernel<<<148 * 16, 256, 0, s>>>(XtY, rows, n_list, V, Dp, sX, planes);
     return cudaGetLastError();
 }
 
@@ -252,6 +266,29 @@ cudaError_t launch_slice_zt(const CentreTask* tasks, int n_tasks, int kp_max, co
 // ---------------------------------------------------------------------------------------------------------------
 // the GEMM
 // ---------------------------------------------------------------------------------------------------------------
+// The digit-pair MMAs of one ring step (64 neighbours) for the three weights W_HI, W_HI - 1, W_HI - 2; fully unrolled, so
+// every shared-memory offset is an immediate.  base0 holds planes 0-2 of both operands, base1 planes 3-5.
+template <int W_HI>
+__device__ __forceinline__ void issue_pairs(uint32_t tmem_base, uint32_t base0, uint32_t base1, uint32_t idesc, uint32_t& started) {
+#pragma unroll
+    for (int w = W_HI; w > W_HI - 3; --w) {
+        const uint32_t acc = tmem_base + (uint32_t)((w % 3) * ACC_STRIDE);
+#pragma unroll
+        for (int t = 0; t <= w; ++t) {
+            const int u = w - t;
+            if (t >= S || u >= S) continue;
+            const uint32_t a_addr = (t < HALF ? base0 : base1) + (t % HALF) * A_PLANE;
+            const uint32_t b_addr = (u < HALF ? base0 : base1) + HALF * A_PLANE + (u % HALF) * B_PLANE;
+#pragma unroll
+            for (int kk = 0; kk < KS / 32; ++kk) {
+                mma_i8(acc, desc_a_mn_sw128(a_addr + kk * 32 * TM), desc_b_k_sw64(b_addr + kk * 32), idesc,
+                       (started >> (w % 3)) & 1u);
+                started |= 1u << (w % 3);
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
 predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, PredictI8Params prm) {
     extern __shared__ unsigned char smem_dyn[];
@@ -289,17 +326,20 @@ predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
     if (warp < 4) {
       asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-      if (warp == 0) {
-        // ------------------------------------------------ TMA producer ------------------------------------------------
+      if (warp != 1) {
+        // ------------------------------------------------ TMA producers ------------------------------------------------
+        // three warps (0, 2, 3), one digit plane of the slot each: the issue rate of the per-lane gather4 instructions,
+        // not the memory system, bounds a single producer warp (ncu r2 v1: the producer never waits, the MMA warp does)
+        const int pw = warp == 0 ? 0 : warp - 1;
         uint32_t q = 0;
         bool ok = true;
-        for (long item = blockIdx.x; item < n_items && ok; item += gridDim.x) {
+        for (long item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int task_id = (int)(item / n_ft), d0 = (int)(item % n_ft) * TM;
             const CentreTask task = prm.tasks[task_id];
             const int k = task.k, kp = task.kp, nk = kp / KS;
-            __syncwarp();
-            for (int i = lane; i < kp; i += 32) nbr_sm[i] = __ldg(task.nbr + (i < k ? i : 0));
-            __syncwarp();
+            prod_barrier();                                              // the previous item's gathers have read nbr_sm
+            for (int i = pw * 32 + lane; i < kp; i += 96) nbr_sm[i] = __ldg(task.nbr + (i < k ? i : 0));
+            prod_barrier();
             for (int pass = 0; pass < 2 && ok; ++pass) {
                 const int halves = pass == 0 ? 2 : 1;
                 for (int ks = 0; ks < nk && ok; ++ks) {
@@ -311,19 +351,15 @@ predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                             break;
                         }
                         const uint32_t dst = ring + slot * SLOT_BYTES;
-                        if (lane == 0) mbar_expect_tx(full_bar(slot), SLOT_BYTES);
+                        if (pw == 0 && lane == 0) mbar_expect_tx(full_bar(slot), SLOT_BYTES);
                         if (lane < KS / 4) {
                             const int4 r = *reinterpret_cast<const int4*>(nbr_sm + ks * KS + lane * 4);
-#pragma unroll
-                            for (int p = 0; p < HALF; ++p) {
-                                const int off = (half * HALF + p) * prm.V;
-                                tma_gather4(dst + p * A_PLANE + lane * 512, &tmA, full_bar(slot), d0, r.x + off, r.y + off,
-                                            r.z + off, r.w + off);
-                            }
-                        } else if (lane < KS / 4 + HALF) {
-                            const int p = lane - KS / 4;
-                            tma_tile2d(dst + HALF * A_PLANE + p * B_PLANE, &tmB, full_bar(slot), ks * KS,
-                                       (task_id * S + half * HALF + p) * TN);
+                            const int off = (half * HALF + pw) * prm.V;
+                            tma_gather4(dst + pw * A_PLANE + lane * 512, &tmA, full_bar(slot), d0, r.x + off, r.y + off,
+                                        r.z + off, r.w + off);
+                        } else if (lane == KS / 4) {
+                            tma_tile2d(dst + HALF * A_PLANE + pw * B_PLANE, &tmB, full_bar(slot), ks * KS,
+                                       (task_id * S + half * HALF + pw) * TN);
                         }
                     }
                 }
@@ -357,30 +393,17 @@ predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         break;
                     }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    if (lane == 0) {
+                    {
                         const uint32_t base0 = ring + slot0 * SLOT_BYTES, base1 = ring + slot1 * SLOT_BYTES;
-                        for (int w = w_hi; w > w_hi - 3; --w) {
-                            const uint32_t acc = tmem_base + (uint32_t)((w % 3) * ACC_STRIDE);
-                            for (int t = 0; t <= w; ++t) {
-                                const int u = w - t;
-                                if (t >= S || u >= S) continue;
-                                const uint32_t a_addr = (t < HALF ? base0 : base1) + (t % HALF) * A_PLANE;
-                                const uint32_t b_addr = (u < HALF ? base0 : base1) + HALF * A_PLANE + (u % HALF) * B_PLANE;
-#pragma unroll
-                                for (int kk = 0; kk < KS / 32; ++kk) {
-                                    mma_i8(acc, desc_a_mn_sw128(a_addr + kk * 32 * TM), desc_b_k_sw64(b_addr + kk * 32), idesc,
-                                           (started >> (w % 3)) & 1u);
-                                    started |= 1u << (w % 3);
-                                }
-                            }
-                        }
+                        if (pass == 0) issue_pairs<S - 1>(tmem_base, base0, base1, idesc, started);
+                        else issue_pairs<S - 4>(tmem_base, base0, base0, idesc, started);
                         mma_commit(empty_bar(slot0));
                         if (halves == 2) mma_commit(empty_bar(slot1));
                     }
                     __syncwarp();
                     q += halves;
                 }
-                if (ok && lane == 0) mma_commit(tfull_bar);
+                if (ok) mma_commit(tfull_bar);
                 __syncwarp();
             }
         }

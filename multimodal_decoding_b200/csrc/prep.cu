@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(256) prep_tasks_kernel(const int* __restrict__
             atomicOr(bad_index_flag, 2);        // bit 1 = vertex id out of range
             v = 0;
         } else if (i < k && vertex_bad[v]) {
-            atomicOr(bad_index_flag, 4);        // bit 2 = a neighbour's betas hold NaN or infinity
+            // bit 2 = a neighbour's betas hold NaN or infinity; bit 3 = the vertex is outside the active set of mmd_upload_active
+            atomicOr(bad_index_flag, vertex_bad[v] == 2 ? 8 : 4);
         }
         sm[i] = v;
     }

@@ -108,7 +108,12 @@ class Engine:
         return [idx64[offsets[i]:offsets[i + 1]] for i in range(v)]
 
     # -- trials ------------------------------------------------------------------------------
-    def upload(self, X, Y, train_ids, test_ids, imagery_ids, test_is_caption):
+    def upload(self, X, Y, train_ids, test_ids, imagery_ids, test_is_caption, active_vertices=None):
+        """`active_vertices` (optional, ascending vertex ids): the vertices the coming searchlight calls will use
+        (mmd_upload_active: X^T Y rows and digit planes are built for them only).
+
+        Ordering contract for borrowed CUDA tensors: the library reads them on its own non-blocking stream, so the
+        producing torch stream is synchronised here first (see include/mmd_b200.h, mmd_upload)."""
         n_total, n_vertices = X.shape
         if Y.shape[0] != n_total:
             raise ValueError(f"X has {n_total} trials but y has {Y.shape[0]}")
@@ -124,9 +129,16 @@ class Engine:
             raise ValueError("test_is_caption must have one entry per test trial")
         xp, xk = _ptr(X)
         yp, yk = _ptr(Y)
-        self._check(self._lib.mmd_upload(self._h, xp, n_total, n_vertices, yp, int(Y.shape[1]),
-                                         tr.ctypes.data, len(tr), te.ctypes.data, len(te), cap.ctypes.data,
-                                         im.ctypes.data, len(im)))
+        if hasattr(xk, "data_ptr") or hasattr(yk, "data_ptr"):
+            import torch
+            for t in (xk, yk):
+                if hasattr(t, "data_ptr") and t.is_cuda:
+                    torch.cuda.current_stream(t.device).synchronize()     # whatever produced the tensor has finished
+        act = None if active_vertices is None else np.ascontiguousarray(np.asarray(active_vertices, dtype=np.int32))
+        self._check(self._lib.mmd_upload_active(self._h, xp, n_total, n_vertices, yp, int(Y.shape[1]),
+                                                tr.ctypes.data, len(tr), te.ctypes.data, len(te), cap.ctypes.data,
+                                                im.ctypes.data, len(im), None if act is None else act.ctypes.data,
+                                                0 if act is None else len(act)))
         self.n_dims = int(Y.shape[1])
         self.n_eval = len(te) + len(im)
         del xk, yk
@@ -324,4 +336,4 @@ class Engine:
         return {"stage_ms": dict(zip(names, [float(x) for x in ms])), "launches": launches.value,
                 "clusters": clusters.value, "syrk_flops": flops.value, "batches": cnt[0], "core_tasks": cnt[1],
                 "grouped_centres": cnt[2], "sum_shared_prefix": cnt[3], "host_plan_ms": cnt[4] / 1e3,
-                "host_adjacency_h2d_ms": cnt[5] / 1e3, "rerouted_centres": cnt[6], "solve_flops": solve.value}
+                "host_adjacency_h2d_ms": cnt[5] / 1e3, "rerouted_centres": cnt[6], "plan_cache_hits": cnt[7], "solve_flops": solve.value}
