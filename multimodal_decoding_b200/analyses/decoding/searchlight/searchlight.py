@@ -154,6 +154,21 @@ def _scores_to_dicts(scores: np.ndarray) -> np.ndarray:
     return out
 
 
+def _report_flags(scores, flags, first_centre=0):
+    """A centre whose normal matrix was not positive definite has no valid fit here (sklearn would fall back from its
+    Cholesky solver to an SVD solve behind searchlight.py:56; this path has no such fallback): its scores are returned as
+    NaN and the centres are named in a RuntimeWarning -- never a silently wrong number."""
+    bad = np.flatnonzero(np.asarray(flags) != 0)
+    if len(bad):
+        import warnings
+        scores[bad] = np.nan
+        shown = ", ".join(str(first_centre + int(b)) for b in bad[:10]) + (", ..." if len(bad) > 10 else "")
+        warnings.warn(f"searchlight: the normal matrix of {len(bad)} centre(s) is not positive definite (centres {shown}); "
+                      "their scores are NaN.  Use alpha > 0 or drop duplicated / constant vertices.", RuntimeWarning,
+                      stacklevel=3)
+    return scores
+
+
 def _is_ragged(A):
     return not (isinstance(A, np.ndarray) and A.dtype != object and A.ndim == 2)
 
@@ -234,7 +249,8 @@ def custom_group_iter_search_light(list_rows, list_indices, estimator, X, y, tra
                                    thread_id, null_distr_dir=None, shuffled_indices=None):
     """A chunk of centres; returns a list of score dicts (searchlight.py:93-114)."""
     if null_distr_dir is None:
-        scores, _ = search_light_scores(X, y, estimator, list_rows, train_ids, test_ids, imagery_ids)
+        scores, flags = search_light_scores(X, y, estimator, list_rows, train_ids, test_ids, imagery_ids)
+        _report_flags(scores, flags)
     else:
         eng = get_engine()
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
@@ -268,6 +284,7 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
         scores, flags = _null_branch(eng, A[lo:hi], np.arange(lo, hi), _estimator_alpha(estimator), len(imagery_ids),
                                      null_distr_dir, shuffled_indices)
+    _report_flags(scores, flags, lo)
     if verbose:
         print(f"searchlight: centres {lo}..{hi} done on device {get_engine().device}, "
               f"{int(flags.sum())} not positive definite")

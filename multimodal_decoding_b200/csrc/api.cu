@@ -963,15 +963,33 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
             } else {
                 memcpy(dst + lo, src32 + lo, (hi - lo) * sizeof(int32_t));
             }
-            uint64_t a = 0x9e3779b97f4a7c15ull ^ lo, b = 0xc2b2ae3d27d4eb4full + lo;
-            for (size_t i = lo; i < hi; ++i) {
-                const uint64_t v = (uint32_t)dst[i];
-                a = (a ^ v) * 0x100000001b3ull;
-                b = (b + v) * 0xff51afd7ed558ccdull;
-                b ^= b >> 29;
+            // two independent 64-bit hashes of the segment; four interleaved lanes each so the multiplies pipeline
+            uint64_t a[4], b[4];
+            for (int j = 0; j < 4; ++j) {
+                a[j] = 0x9e3779b97f4a7c15ull ^ (lo + j);
+                b[j] = 0xc2b2ae3d27d4eb4full + 31 * (lo + j);
             }
-            part1[t] = a;
-            part2[t] = b;
+            size_t i = lo;
+            for (; i + 8 <= hi; i += 8)
+                for (int j = 0; j < 4; ++j) {
+                    const uint64_t v = (uint64_t)(uint32_t)dst[i + 2 * j] | ((uint64_t)(uint32_t)dst[i + 2 * j + 1] << 32);
+                    a[j] = (a[j] ^ v) * 0x100000001b3ull;
+                    b[j] = (b[j] + v) * 0xff51afd7ed558ccdull;
+                    b[j] ^= b[j] >> 29;
+                }
+            for (; i < hi; ++i) {
+                const uint64_t v = (uint32_t)dst[i];
+                a[0] = (a[0] ^ v) * 0x100000001b3ull;
+                b[0] = (b[0] + v) * 0xff51afd7ed558ccdull;
+                b[0] ^= b[0] >> 29;
+            }
+            uint64_t ha = 0, hb = 0;
+            for (int j = 0; j < 4; ++j) {
+                ha = (ha ^ a[j]) * 0x100000001b3ull;
+                hb = (hb + b[j]) * 0xff51afd7ed558ccdull;
+            }
+            part1[t] = ha;
+            part2[t] = hb;
         };
         std::vector<std::thread> pool;
         for (int t = 1; t < nt; ++t) pool.emplace_back(conv, t);

@@ -448,7 +448,7 @@ predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                         for (int qq = 0; qq < 3; ++qq) {
                             const double wt = __longlong_as_double((long long)(1023 - (12 + 7 * (w_hi - qq))) << 52);   // 2^-(12 + 7 w)
-                            a = __dadd_rn(a, __dmul_rn((double)(int32_t)v[qq][j], wt));
+                            a = fma((double)(int32_t)v[qq][j], wt, a);          // the product with a power of two is exact
                         }
                         // last pass: apply the two power-of-two scales (exact products)
                         if (pass == 1) a = __dmul_rn(__dmul_rn(a, sx), __ldg(sz + ch * 8 + j));
@@ -475,16 +475,30 @@ predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int lo[3] = {0, n_cap, n_test}, hi[3] = {n_cap, n_test, n_eval};
             // (the empty asm statements pin the evaluation order row by row: without them ptxas evaluates all 48 rows
             // speculatively for all three groups and spills)
+            // Rows are handled in blocks of 8; a block that lies inside one prediction group (all but two or three of
+            // the 18 blocks) takes a path without per-row selects.  group_of() is warp-uniform, so are the branches.
+            auto group_of = [&](int e) { return (e >= n_cap) + (e >= n_test) + (e >= n_eval); };
             double part[3] = {0.0, 0.0, 0.0};
 #pragma unroll
-            for (int c = 0; c < EPI_COLS; ++c) {
-                const int e = e0 + c;
-                const int g = (e >= n_cap) + (e >= n_test) + (e >= n_eval);
-                const double v = racc[c];
-                part[0] += g == 0 ? v : 0.0;
-                part[1] += g == 1 ? v : 0.0;
-                part[2] += g == 2 ? v : 0.0;
-                asm volatile("" : "+d"(part[0]), "+d"(part[1]), "+d"(part[2]));
+            for (int b = 0; b < EPI_COLS / 8; ++b) {
+                const int g_lo = group_of(e0 + b * 8), g_hi = group_of(e0 + b * 8 + 7);
+                if (g_lo == g_hi) {
+                    double t = 0.0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) t += racc[b * 8 + j];
+                    if (g_lo == 0) part[0] += t;
+                    else if (g_lo == 1) part[1] += t;
+                    else if (g_lo == 2) part[2] += t;
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int g = group_of(e0 + b * 8 + j);
+                        const double v = racc[b * 8 + j];
+                        part[0] += g == 0 ? v : 0.0;
+                        part[1] += g == 1 ? v : 0.0;
+                        part[2] += g == 2 ? v : 0.0;
+                    }
+                }
             }
 #pragma unroll
             for (int g = 0; g < 3; ++g) red[(cg * 3 + g) * TM + f] = part[g];
@@ -498,15 +512,30 @@ predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             }
             epi_barrier();
 #pragma unroll
-            for (int c = 0; c < EPI_COLS; ++c) {
-                const int e = e0 + c;
-                const int g = (e >= n_cap) + (e >= n_test) + (e >= n_eval);
-                const double t = racc[c] - (g == 0 ? mu[0] : g == 1 ? mu[1] : mu[2]);
-                const double t2 = t * t;
-                part[0] += g == 0 ? t2 : 0.0;
-                part[1] += g == 1 ? t2 : 0.0;
-                part[2] += g == 2 ? t2 : 0.0;
-                asm volatile("" : "+d"(part[0]), "+d"(part[1]), "+d"(part[2]));
+            for (int b = 0; b < EPI_COLS / 8; ++b) {
+                const int g_lo = group_of(e0 + b * 8), g_hi = group_of(e0 + b * 8 + 7);
+                if (g_lo == g_hi) {
+                    const double m = g_lo == 0 ? mu[0] : g_lo == 1 ? mu[1] : mu[2];
+                    double t2 = 0.0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const double t = racc[b * 8 + j] - m;
+                        t2 = fma(t, t, t2);
+                    }
+                    if (g_lo == 0) part[0] += t2;
+                    else if (g_lo == 1) part[1] += t2;
+                    else if (g_lo == 2) part[2] += t2;
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int g = group_of(e0 + b * 8 + j);
+                        const double t = racc[b * 8 + j] - (g == 0 ? mu[0] : g == 1 ? mu[1] : mu[2]);
+                        const double t2 = t * t;
+                        part[0] += g == 0 ? t2 : 0.0;
+                        part[1] += g == 1 ? t2 : 0.0;
+                        part[2] += g == 2 ? t2 : 0.0;
+                    }
+                }
             }
 #pragma unroll
             for (int g = 0; g < 3; ++g) red[(cg * 3 + g) * TM + f] = part[g];
@@ -517,18 +546,24 @@ predict_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 sd[g] = n_g > 0 ? sqrt(((red[g * TM + f] + red[(3 + g) * TM + f]) + red[(6 + g) * TM + f]) / n_g) : 0.0;
                 rs[g] = sd[g] == 0.0 ? 1.0 : 1.0 / sd[g];
             }
-            {
-                double* o = out + (long)e0 * prm.Dp;                         // running pointers: one live address, not 48
-                double* oraw = out + (long)(EVAL_PAD + e0 - n_test) * prm.Dp;
 #pragma unroll
-                for (int c = 0; c < EPI_COLS; ++c, o += prm.Dp, oraw += prm.Dp) {
-                    const int e = e0 + c;
-                    const int g = (e >= n_cap) + (e >= n_test) + (e >= n_eval);
-                    const double raw = racc[c];
-                    const double z = (raw - (g == 0 ? mu[0] : g == 1 ? mu[1] : mu[2])) * (g == 0 ? rs[0] : g == 1 ? rs[1] : rs[2]);
-                    *o = g < 3 ? z : 0.0;                                    // rows n_eval .. 143 are written as zero
-                    if (g == 2) *oraw = raw;                                 // *_no_std scores
-                    asm volatile("" ::"l"(o) : "memory");
+            for (int b = 0; b < EPI_COLS / 8; ++b) {
+                const int eb = e0 + b * 8;
+                const int g_lo = group_of(eb), g_hi = group_of(eb + 7);
+                double* o = out + (long)eb * prm.Dp;
+                if (g_lo == g_hi && g_lo < 2) {
+                    const double m = g_lo == 0 ? mu[0] : mu[1], r = g_lo == 0 ? rs[0] : rs[1];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) o[(long)j * prm.Dp] = (racc[b * 8 + j] - m) * r;
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int g = group_of(eb + j);
+                        const double raw = racc[b * 8 + j];
+                        const double z = (raw - (g == 0 ? mu[0] : g == 1 ? mu[1] : mu[2])) * (g == 0 ? rs[0] : g == 1 ? rs[1] : rs[2]);
+                        o[(long)j * prm.Dp] = g < 3 ? z : 0.0;                                   // rows n_eval .. 143 are written as zero
+                        if (g == 2) out[(long)(EVAL_PAD + eb + j - n_test) * prm.Dp] = raw;       // *_no_std scores
+                    }
                 }
             }
             if (cg == 0) {

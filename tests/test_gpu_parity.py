@@ -329,6 +329,23 @@ def test_neighbourhood_and_feature_sweep(engine, k, n_dims):
     assert np.array_equal(got[sample], want)
 
 
+def test_knn_k1500_on_the_level7_mesh(engine):
+    """k = 1500 (BASELINE.json configs[3]) on the full-size mesh (163,842 vertices): the radix-select keeps at most 2048
+    candidates per query, so the call must not report an overflow on a near-regular mesh, and the rows equal brute force."""
+    from multimodal_decoding_b200 import synthetic as syn
+    mesh = syn.make_mesh(level=7, seed=7)
+    coords = np.asarray(mesh.coords, dtype=np.float64)
+    V = len(coords)
+    for lo, hi in ((0, 4096), (V - 2048, V)):                  # coarse-level and finest-level vertices
+        dist, idx = engine.knn(coords, 1500, lo, hi)           # raises RuntimeError on overflow
+        for q in (lo, lo + 1777, hi - 1):
+            d2 = ((coords - coords[q]) ** 2).sum(axis=1)
+            order = np.lexsort((np.arange(V), d2))[:1500]
+            assert np.array_equal(np.sort(idx[q - lo]), np.sort(order))
+            assert np.allclose(dist[q - lo], np.sqrt(d2[idx[q - lo]]), rtol=1e-12, atol=0)
+            assert np.all(np.diff(dist[q - lo]) >= 0)
+
+
 def test_full_hemisphere_sharing_invariance(engine):
     """BASELINE.json configs[1] at full size (163,842 vertices, k=750, N_train=4000, D=1024): the score maps with and
     without prefix sharing (different elimination orders of the same normal equations) agree within the north star's
