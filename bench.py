@@ -409,6 +409,8 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
         cps = min(cps, min(b - a for a, b in split_bounds(V, world)))
     n_rows = min(hi - lo, (W + K) * cps)
     A = A_all[lo:lo + n_rows]
+    # strong scaling through the public call: every rank holds the whole (Morton-ordered) adjacency and takes its own range
+    A_full = A_all if (not weak and args.centres_per_step == 0) else None
     del A_all
     is_cap = np.arange(140) < 70
     estimator = Ridge(alpha=1.0, fit_intercept=False)
@@ -466,7 +468,9 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
             rows = rows_of(step)
             if weak:                            # n_jobs=1: the whole job on this process's GPU, no collective
                 return sl.custom_search_light(Xh, Yh, estimator, rows, ids[0], ids[1], ids[2], n_jobs=1)
-            full = np.zeros((world * cps, k), dtype=np.int64)   # custom_search_light takes the r-th range itself
+            if A_full is not None:              # custom_search_light takes the r-th range of the hemisphere itself
+                return sl.custom_search_light(Xh, Yh, estimator, A_full, ids[0], ids[1], ids[2], n_jobs=world)
+            full = np.zeros((world * cps, k), dtype=np.int64)
             full[rank * cps:(rank + 1) * cps] = rows
             return sl.custom_search_light(Xh, Yh, estimator, full, ids[0], ids[1], ids[2], n_jobs=world)
 
@@ -478,9 +482,10 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
             out = e2e_step(s)
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
-        assert len(out) == (cps if weak else world * cps) and len(out[0]) == 8
+        assert len(out) == (cps if weak else (V if A_full is not None else world * cps)) and len(out[0]) == 8
         h2d = Xh.nbytes + Yh.nbytes + cps * k * 4
-        e2e = {"value": round(world * cps * K / e2e_s, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+        n_e2e = V if A_full is not None else world * cps
+        e2e = {"value": round(n_e2e * K / e2e_s, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(cps * (8 * 8 + 4)), "ms_per_step": round(e2e_s / K * 1e3, 2),
                "api": "custom_search_light(X_host_f16, y_host_f16, Ridge(alpha=1), A_rows, ...)"}
     else:

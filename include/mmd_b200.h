@@ -94,6 +94,9 @@ int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const 
  * the vertices the rank's neighbourhoods use.  X^T Y rows and the digit planes of the integer prediction GEMM are built
  * for those vertices only (the per-upload work shrinks with the shard); a later searchlight call whose neighbourhoods
  * leave the set fails with a message naming mmd_upload_active. */
+/* Host helper for the list above: mask[v] = 1 for every vertex id that occurs in `indices` (n entries; int64 when is_i64,
+ * else int32), 0 elsewhere; returns 2 when an id is outside [0, n_vertices).  Runs on host threads. */
+int mmd_mark_vertices(const void* indices, int is_i64, int64_t n, int n_vertices, uint8_t* mask);
 int mmd_upload_active(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
                       const int32_t* train_ids, int n_train, const int32_t* test_ids, int n_test,
                       const uint8_t* test_is_caption, const int32_t* imagery_ids, int n_imagery,
@@ -157,6 +160,22 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
  * (A = G - G_f + alpha I); the validation trials run through the solver in chunks of 144 right-hand sides. */
 int mmd_searchlight_cv(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, const double* alphas, int n_alphas,
                        const int32_t* fold_bounds, int n_folds, double* fold_scores_out, int32_t* flags_out);
+
+/* Whole-brain ridge decoder with an alpha grid and K-fold cross-validation: the computation behind
+ *   GridSearchCV(Ridge(fit_intercept=False), param_grid=dict(alpha=...), scoring=make_scorer(pairwise_accuracy), cv=5, refit=True)
+ *   .fit(train_fmri_betas, train_latents)                                       ridge_regression_decoding.py:111-123
+ * on this library's own float64 kernels (csrc/dense.cu: DMMA GEMM, blocked Cholesky, triangular solves; no BLAS / LAPACK).
+ *   mmd_ridge_load     X (n x v) and Y (n x d), HOST or DEVICE, float32 (is_f32 = 1) or float64, row-major.  Forms X X^T (n x n)
+ *                      when v > n -- sklearn's kernel form of the cholesky solver -- else X^T X and X^T Y.
+ *   mmd_ridge_cv       fold_scores_out (n_alphas x n_folds) = cv_results_["split<f>_test_score"][a]: ridge fitted without fold f
+ *                      (contiguous folds, fold_bounds as in mmd_searchlight_cv), pairwise_accuracy(Y_val, X_val W) (eval.py:116-123)
+ *   mmd_ridge_fit      refit on all trials; coef_out (d x v) float64 HOST = sklearn's coef_ (may be NULL); the weights stay on the
+ *                      device for mmd_ridge_predict
+ *   mmd_ridge_predict  out (m x d) float64 HOST = X_new W for X_new (m x v) */
+int mmd_ridge_load(mmd_handle* h, const void* X, int x_is_f32, int n, int v, const void* Y, int y_is_f32, int d);
+int mmd_ridge_cv(mmd_handle* h, const double* alphas, int n_alphas, const int32_t* fold_bounds, int n_folds, double* fold_scores_out);
+int mmd_ridge_fit(mmd_handle* h, double alpha, double* coef_out);
+int mmd_ridge_predict(mmd_handle* h, const void* X, int x_is_f32, int m, double* out);
 
 /* eval.py primitives for arbitrary shapes, HOST float64 row-major buffers.
  *   mmd_cosine_distances          get_distance_matrix(predictions, originals, "cosine")   eval.py:103-104

@@ -65,64 +65,57 @@ def kfold_bounds(n, n_splits=NUM_CV_SPLITS):
 
 
 class RidgeGPU:
-    """The fitted-estimator protocol the reference relies on (`.alpha`, `.fit_intercept`, `.coef_ (D x V)`, `.predict`)."""
+    """The fitted-estimator protocol the reference relies on (`.alpha`, `.fit_intercept`, `.coef_ (D x V)`, `.predict`).
+    The weights stay on the GPU (mmd_ridge_fit); `predict` runs the library's float64 GEMM (mmd_ridge_predict).  The engine
+    holds one fitted ridge at a time: a later grid search on the same engine replaces it."""
     fit_intercept = False
 
-    def __init__(self, alpha, coef, device):
-        self.alpha, self._coef, self._device = alpha, coef, device           # coef: (V x D) float64 on the GPU
+    def __init__(self, alpha, engine, token):
+        self.alpha, self._eng, self._token = alpha, engine, token
+        self._coef = None
+
+    def _check_live(self):
+        if getattr(self._eng, "_ridge_token", None) is not self._token:
+            raise RuntimeError("this RidgeGPU's weights were replaced by a later grid search on the same engine")
 
     @property
     def coef_(self):
-        return self._coef.T.cpu().numpy()
+        if self._coef is None:
+            self._check_live()
+            self._coef = self._eng.ridge_fit(self.alpha, want_coef=True)
+        return self._coef
 
     def predict(self, X):
-        import torch
-        x = torch.as_tensor(np.asarray(X), dtype=torch.float64, device=self._device)
-        return (x @ self._coef).cpu().numpy()
+        self._check_live()
+        return self._eng.ridge_predict(X)
 
 
 def grid_search_ridge_gpu(X, Y, alphas, n_splits=NUM_CV_SPLITS, device=None, verbose=0):
-    """GridSearchCV(...).fit(X, Y) semantics; returns (best_alpha, mean_test_score per alpha, RidgeGPU refit)."""
-    import torch
+    """GridSearchCV(...).fit(X, Y) semantics; returns (best_alpha, mean_test_score per alpha, RidgeGPU refit).
+
+    Everything numeric runs in libmmd_b200.so (csrc/dense.cu): the Gram matrix (kernel form X X^T when there are more voxels
+    than trials, like sklearn's cholesky solver, else X^T X), per fold and alpha a blocked Cholesky factorisation and the
+    triangular solves for all targets, the validation predictions and their pairwise accuracy; fold matrices are sub-blocks
+    (or down-dates) of the one Gram matrix."""
     from ..decoding.searchlight.searchlight import get_engine
     eng = get_engine(device)
-    dev = torch.device("cuda", eng.device)
-    x = torch.as_tensor(np.asarray(X), dtype=torch.float64, device=dev)
-    y = torch.as_tensor(np.asarray(Y), dtype=torch.float64, device=dev)
-    n, v = x.shape
+    n = len(X)
     if n < n_splits:
         raise ValueError(f"Cannot have number of splits n_splits={n_splits} greater than the number of samples: n_samples={n}.")
-    dual = v > n
-    gram = x @ x.T if dual else x.T @ x                  # K (n x n) or XtX (v x v)
-    xty = None if dual else x.T @ y
-    eye = torch.eye(gram.shape[0], dtype=torch.float64, device=dev)
-    y_host = np.asarray(Y, dtype=np.float64)
-    scores = np.zeros((len(alphas), n_splits))
-    for f, (lo, hi) in enumerate(kfold_bounds(n, n_splits)):
-        tr = torch.cat([torch.arange(0, lo, device=dev), torch.arange(hi, n, device=dev)])
-        if dual:
-            k_tr, k_val, y_tr = gram[tr][:, tr], gram[lo:hi][:, tr], y[tr]
-        else:                                            # fold Gram by subtraction: XtX - X_f^T X_f
-            xf = x[lo:hi]
-            g_tr, b_tr = gram - xf.T @ xf, xty - xf.T @ y[lo:hi]
-        for a, alpha in enumerate(alphas):
-            if dual:
-                chol = torch.linalg.cholesky(k_tr + alpha * eye[: len(tr), : len(tr)])
-                pred = k_val @ torch.cholesky_solve(y_tr, chol)
-            else:
-                chol = torch.linalg.cholesky(g_tr + alpha * eye)
-                pred = x[lo:hi] @ torch.cholesky_solve(b_tr, chol)
-            scores[a, f] = eng.pairwise_accuracy(y_host[lo:hi], pred.cpu().numpy(), False, False)
-            if verbose:
+    alphas = [float(a) for a in alphas]
+    eng.ridge_load(X, Y)
+    bounds = [0] + [hi for _, hi in kfold_bounds(n, n_splits)]
+    scores = eng.ridge_cv(alphas, bounds)                 # (n_alphas, n_splits)
+    if verbose:
+        for f in range(n_splits):
+            for a, alpha in enumerate(alphas):
                 print(f"[CV {f + 1}/{n_splits}] END alpha={alpha};, score={scores[a, f]:.3f}")
-    mean = scores.mean(axis=1)
+    mean = np.average(scores, axis=1)                     # _search.py: array_means
     best = int(np.argmax(mean))                          # first maximum = rank-"min" tie break of GridSearchCV
     alpha = alphas[best]
-    if dual:
-        coef = x.T @ torch.cholesky_solve(y, torch.linalg.cholesky(gram + alpha * eye))
-    else:
-        coef = torch.cholesky_solve(xty, torch.linalg.cholesky(gram + alpha * eye))
-    return alpha, mean, RidgeGPU(alpha, coef, dev)
+    eng.ridge_fit(alpha, want_coef=False)
+    eng._ridge_token = token = object()
+    return alpha, mean, RidgeGPU(alpha, eng, token)
 
 
 def run(args):

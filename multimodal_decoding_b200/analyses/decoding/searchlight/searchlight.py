@@ -193,12 +193,17 @@ def _require_rectangular(A, what):
 
 def _active_vertices(A, n_vertices):
     """Ascending ids of the vertices the neighbourhoods in `A` use; None when that is (nearly) all of them."""
-    mask = np.zeros(n_vertices, dtype=bool)
+    from .... import _lib
+    mask = np.zeros(n_vertices, dtype=np.uint8)
     if _is_ragged(A):
-        for r in A:
-            mask[np.asarray(r)] = True
+        flat = np.ascontiguousarray(np.concatenate([np.asarray(r).ravel() for r in A]))
     else:
-        mask[np.asarray(A).ravel()] = True
+        flat = np.ascontiguousarray(A)
+    if flat.dtype not in (np.int32, np.int64):
+        flat = flat.astype(np.int64)
+    rc = _lib.load().mmd_mark_vertices(flat.ctypes.data, int(flat.dtype == np.int64), flat.size, n_vertices, mask.ctypes.data)
+    if rc == 2:
+        raise ValueError(f"adjacency holds a vertex index outside [0, {n_vertices})")
     active = np.flatnonzero(mask)
     return None if len(active) > 0.9 * n_vertices else active
 
@@ -216,7 +221,13 @@ def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *,
             is_caption = _is_caption_mask(len(test_ids))
         # a rank of a vertex-sharded call stages the cross-covariance rows of its own neighbourhoods only
         active = _active_vertices(A, np.shape(X)[1]) if shard_only and len(A) else None
-        eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption, active_vertices=active)
+        Xd = _as_f16(X, "X")
+        if shard_only and isinstance(Xd, np.ndarray):
+            # every rank holds the same host X: each copies 1/N of its rows over PCIe, NVLink carries the rest
+            from ....sharding import device_copy_via_peers
+            Xpeer = device_copy_via_peers(Xd)
+            Xd = Xd if Xpeer is None else Xpeer
+        eng.upload(Xd, _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption, active_vertices=active)
     if grid:
         return search_light_cv(eng, A, grid[0], grid[1], len(train_ids))[:2]
     if _is_ragged(A):

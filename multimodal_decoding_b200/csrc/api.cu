@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -150,6 +151,18 @@ struct CvState {
     }
 };
 
+// Whole-brain ridge grid search state (mmd_ridge_*; dense.cu): padded float64 panels of one (X, Y) problem.
+struct RidgeState {
+    int n = 0, v = 0, d = 0, np = 0, vp = 0, dp = 0, mp_fit = 0;
+    bool dual = false, loaded = false, fitted = false;
+    DevBuf X, Xt, Y, Yt, G, bt, A, Lt, linv, linvT, rhs, kval, pred_t, pred, yval, idx_tr, idx_val, flag, coef_t, stage, xft, yft,
+        dist, sq, count;
+    std::vector<DevBuf*> all() {
+        return {&X, &Xt, &Y, &Yt, &G, &bt, &A, &Lt, &linv, &linvT, &rhs, &kval, &pred_t, &pred, &yval, &idx_tr, &idx_val, &flag,
+                &coef_t, &stage, &xft, &yft, &dist, &sq, &count};
+    }
+};
+
 struct mmd_handle {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -174,6 +187,7 @@ struct mmd_handle {
     // their scales, the score kernel's tolerance input, the list of centres handed back to the float64 kernels
     DevBuf xplanes, sX, colmax, zplanes, sZ, amp2, i8_status, reroute_list, reroute_counts, margins;
     CvState* cv = nullptr;          // non-null while mmd_searchlight_cv runs
+    RidgeState* ridge = nullptr;    // mmd_ridge_load
     struct PlanCache* plan_cache = nullptr;     // clusters / unions / groups of the last adjacency (run_searchlight)
     int64_t plan_hits = 0;
     int predict_mode = 1;           // 1: tcgen05 int8 digit GEMM + float64 reroute of guarded centres; 0: float64 DMMA kernel
@@ -1215,6 +1229,10 @@ void mmd_destroy(mmd_handle* h) {
     if (h->up_copied) cudaEventDestroy(h->up_copied);
     h->adj_host.release();
     delete h->plan_cache;
+    if (h->ridge) {
+        for (DevBuf* b : h->ridge->all()) b->release();
+        delete h->ridge;
+    }
     for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
     cudaStreamDestroy(h->stream);
     delete h;
@@ -1434,6 +1452,28 @@ int mmd_radius_neighbors(mmd_handle* h, const double* coords, int n_vertices, do
     dout.release();
     doff.release();
     return rc;
+}
+
+// Host helper of the vertex-sharded path: mask[v] = 1 for every vertex id in `indices` (n entries, int64 when is_i64 else
+// int32), by host threads.  What np.unique(A[lo:hi]) computes, without the sort (custom_search_light under sharding).
+int mmd_mark_vertices(const void* indices, int is_i64, int64_t n, int n_vertices, uint8_t* mask) {
+    if (!indices || !mask || n < 0 || n_vertices < 1) return 1;
+    memset(mask, 0, (size_t)n_vertices);
+    int nt = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<unsigned>(std::thread::hardware_concurrency(), 32u), n / (1 << 20) + 1));
+    std::atomic<int> bad(0);
+    auto work = [&](int t) {
+        const int64_t lo = n * t / nt, hi = n * (t + 1) / nt;
+        for (int64_t i = lo; i < hi; ++i) {
+            const int64_t v = is_i64 ? reinterpret_cast<const int64_t*>(indices)[i] : reinterpret_cast<const int32_t*>(indices)[i];
+            if (v < 0 || v >= n_vertices) bad.store(1);
+            else mask[v] = 1;                               // racing writers store the same value
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < nt; ++t) pool.emplace_back(work, t);
+    work(0);
+    for (auto& t : pool) t.join();
+    return bad.load() ? 2 : 0;
 }
 
 int mmd_upload(mmd_handle* h, const void* X, int n_total, int n_vertices, const void* Y, int n_dims,
@@ -1794,6 +1834,248 @@ int mmd_searchlight_cv(mmd_handle* h, const int32_t* adjacency, int n_centres, i
                 const size_t o = ((size_t)i * n_alphas + a) * n_folds + f;
                 fold_scores_out[o] = den > 0 ? (double)counts[o] / (double)den : std::nan("");
             }
+    return 0;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// whole-brain ridge: load / cross-validate / fit / predict (ridge_regression_decoding.py:111-135)
+// ------------------------------------------------------------------------------------------
+namespace {
+
+// One ridge solve on the loaded problem without the trials `val` (empty = all trials), regulariser alpha.
+// Leaves the TRANSPOSED solution in r.rhs: dual form (dp x mp) dual coefficients over the remaining trials `tr`,
+// primal form (dp x vp) weights.  mp_out = padded order of the factored matrix.
+int ridge_solve(mmd_handle* h, RidgeState& r, const std::vector<int>& tr, const std::vector<int>& val, double alpha, int* mp_out) {
+    const int n_tr = (int)tr.size(), n_val = (int)val.size();
+    if (to_device(h, r.idx_tr, tr.data(), tr.size())) return 1;
+    if (to_device(h, r.idx_val, val.data(), val.size())) return 1;
+    CU(cudaStreamSynchronize(h->stream));                       // the index vectors are pageable
+    const int mp = r.dual ? round_up(n_tr, NB) : r.vp;
+    *mp_out = mp;
+    CU(r.A.ensure((size_t)mp * mp * sizeof(double)));
+    CU(r.Lt.ensure((size_t)mp * mp * sizeof(double)));
+    CU(r.linv.ensure((size_t)mp * NB * sizeof(double)));
+    CU(r.linvT.ensure((size_t)mp * NB * sizeof(double)));
+    CU(r.rhs.ensure((size_t)r.dp * mp * sizeof(double)));
+    CU(r.flag.ensure(sizeof(int)));
+    if (r.dual) {
+        // K[tr, tr] + alpha I ; right-hand sides Y[tr]^T
+        CU(launch_gather_block(r.G.as<double>(), r.np, r.idx_tr.as<int>(), n_tr, r.idx_tr.as<int>(), n_tr, r.A.as<double>(), mp, mp,
+                               alpha, 1.0, h->stream));
+        CU(launch_gather_block(r.Yt.as<double>(), r.np, nullptr, r.dp, r.idx_tr.as<int>(), n_tr, r.rhs.as<double>(), r.dp, mp, 0.0,
+                               0.0, h->stream));
+        h->launches += 2;
+    } else {
+        // X^T X - Xf^T Xf + alpha I ; right-hand sides (X^T Y - Xf^T Yf)^T
+        CU(launch_gather_block(r.G.as<double>(), r.vp, nullptr, r.v, nullptr, r.v, r.A.as<double>(), mp, mp, alpha, 1.0, h->stream));
+        CU(cudaMemcpyAsync(r.rhs.p, r.bt.p, (size_t)r.dp * mp * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        h->launches += 1;
+        if (n_val > 0) {
+            const int kv = round_up(n_val, 16);
+            CU(r.xft.ensure((size_t)r.vp * kv * sizeof(double)));
+            CU(r.yft.ensure((size_t)r.dp * kv * sizeof(double)));
+            CU(launch_gather_block(r.Xt.as<double>(), r.np, nullptr, r.vp, r.idx_val.as<int>(), n_val, r.xft.as<double>(), r.vp, kv,
+                                   0.0, 0.0, h->stream));
+            CU(launch_gather_block(r.Yt.as<double>(), r.np, nullptr, r.dp, r.idx_val.as<int>(), n_val, r.yft.as<double>(), r.dp, kv,
+                                   0.0, 0.0, h->stream));
+            DenseGemm g{};
+            g.A = g.B = r.xft.as<double>(); g.lda = g.ldb = kv; g.C = r.A.as<double>(); g.ldc = mp;
+            g.M = g.N = mp; g.K = kv; g.mode = 1; g.lower_only = 1;
+            CU(launch_dense_gemm(g, h->stream));
+            DenseGemm b{};
+            b.A = r.yft.as<double>(); b.lda = kv; b.B = r.xft.as<double>(); b.ldb = kv; b.C = r.rhs.as<double>(); b.ldc = mp;
+            b.M = r.dp; b.N = mp; b.K = kv; b.mode = 1;
+            CU(launch_dense_gemm(b, h->stream));
+            h->launches += 4;
+        }
+    }
+    CU(cudaMemsetAsync(r.flag.p, 0, sizeof(int), h->stream));
+    CU(dense_potrf(r.A.as<double>(), mp, r.linv.as<double>(), r.linvT.as<double>(), r.flag.as<int>(), h->stream));
+    CU(launch_transpose_f64(r.A.as<double>(), mp, mp, mp, r.Lt.as<double>(), mp, mp, h->stream));
+    CU(dense_potrs_t(r.A.as<double>(), r.Lt.as<double>(), r.linv.as<double>(), r.linvT.as<double>(), mp, r.rhs.as<double>(), r.dp,
+                     h->stream));
+    h->launches += 7 * (mp / NB) + 1;
+    return 0;
+}
+
+// predictions of the solution in r.rhs for the trials `val` -> r.pred (n_val x dp)
+int ridge_predict_val(mmd_handle* h, RidgeState& r, int n_tr, int n_val, int mp) {
+    const int nvp = round_up(n_val, NB);
+    CU(r.pred_t.ensure((size_t)r.dp * nvp * sizeof(double)));
+    CU(r.pred.ensure((size_t)nvp * r.dp * sizeof(double)));
+    CU(r.kval.ensure((size_t)nvp * mp * sizeof(double)));
+    if (r.dual)      // K[val, tr]
+        CU(launch_gather_block(r.G.as<double>(), r.np, r.idx_val.as<int>(), n_val, r.idx_tr.as<int>(), n_tr, r.kval.as<double>(), nvp,
+                               mp, 0.0, 0.0, h->stream));
+    else             // X[val]
+        CU(launch_gather_block(r.X.as<double>(), r.vp, r.idx_val.as<int>(), n_val, nullptr, r.vp, r.kval.as<double>(), nvp, mp, 0.0,
+                               0.0, h->stream));
+    DenseGemm g{};
+    g.A = r.rhs.as<double>(); g.lda = mp; g.B = r.kval.as<double>(); g.ldb = mp; g.C = r.pred_t.as<double>(); g.ldc = nvp;
+    g.M = r.dp; g.N = n_val; g.K = mp;
+    CU(launch_dense_gemm(g, h->stream));
+    CU(launch_transpose_f64(r.pred_t.as<double>(), nvp, r.dp, n_val, r.pred.as<double>(), r.dp, nvp, h->stream));
+    h->launches += 3;
+    return 0;
+}
+
+}  // namespace
+
+int mmd_ridge_load(mmd_handle* h, const void* X, int x_is_f32, int n, int v, const void* Y, int y_is_f32, int d) {
+    if (!h) return 1;
+    if (!X || !Y || n < 1 || v < 1 || d < 1) return fail(h, "mmd_ridge_load: bad arguments");
+    CU(cudaSetDevice(h->device));
+    if (!h->ridge) h->ridge = new RidgeState();
+    RidgeState& r = *h->ridge;
+    r.loaded = r.fitted = false;
+    r.n = n; r.v = v; r.d = d;
+    r.np = round_up(n, NB); r.vp = round_up(v, NB); r.dp = round_up(d, NB);
+    r.dual = v > n;                                     // sklearn's cholesky solver: kernel form when n_features > n_samples
+    CU(r.X.ensure((size_t)r.np * r.vp * sizeof(double)));
+    CU(r.Xt.ensure((size_t)r.vp * r.np * sizeof(double)));
+    CU(r.Y.ensure((size_t)r.np * r.dp * sizeof(double)));
+    CU(r.Yt.ensure((size_t)r.dp * r.np * sizeof(double)));
+    const size_t xb = (size_t)n * v * (x_is_f32 ? 4 : 8), yb = (size_t)n * d * (y_is_f32 ? 4 : 8);
+    CU(r.stage.ensure(std::max(xb, yb)));
+    span_begin(h, ST_XTY);
+    CU(cudaMemcpyAsync(r.stage.p, X, xb, cudaMemcpyDefault, h->stream));
+    CU(launch_widen_pad(r.stage.p, x_is_f32, v, n, v, r.X.as<double>(), r.np, r.vp, h->stream));
+    CU(cudaMemcpyAsync(r.stage.p, Y, yb, cudaMemcpyDefault, h->stream));
+    CU(launch_widen_pad(r.stage.p, y_is_f32, d, n, d, r.Y.as<double>(), r.np, r.dp, h->stream));
+    CU(launch_transpose_f64(r.X.as<double>(), r.vp, r.np, r.vp, r.Xt.as<double>(), r.np, r.vp, h->stream));
+    CU(launch_transpose_f64(r.Y.as<double>(), r.dp, r.np, r.dp, r.Yt.as<double>(), r.np, r.dp, h->stream));
+    DenseGemm g{};
+    if (r.dual) {                                       // K = X X^T
+        CU(r.G.ensure((size_t)r.np * r.np * sizeof(double)));
+        g.A = g.B = r.X.as<double>(); g.lda = g.ldb = r.vp; g.C = r.G.as<double>(); g.ldc = r.np; g.M = g.N = r.np; g.K = r.vp;
+        CU(launch_dense_gemm(g, h->stream));
+    } else {                                            // X^T X and (X^T Y)^T
+        CU(r.G.ensure((size_t)r.vp * r.vp * sizeof(double)));
+        CU(r.bt.ensure((size_t)r.dp * r.vp * sizeof(double)));
+        g.A = g.B = r.Xt.as<double>(); g.lda = g.ldb = r.np; g.C = r.G.as<double>(); g.ldc = r.vp; g.M = g.N = r.vp; g.K = r.np;
+        CU(launch_dense_gemm(g, h->stream));
+        DenseGemm b{};
+        b.A = r.Yt.as<double>(); b.lda = r.np; b.B = r.Xt.as<double>(); b.ldb = r.np; b.C = r.bt.as<double>(); b.ldc = r.vp;
+        b.M = r.dp; b.N = r.vp; b.K = r.np;
+        CU(launch_dense_gemm(b, h->stream));
+    }
+    span_end(h, 6);
+    CU(cudaStreamSynchronize(h->stream));
+    resolve_spans(h);
+    r.loaded = true;
+    return 0;
+}
+
+int mmd_ridge_cv(mmd_handle* h, const double* alphas, int n_alphas, const int32_t* fold_bounds, int n_folds, double* fold_scores_out) {
+    if (!h) return 1;
+    if (!h->ridge || !h->ridge->loaded) return fail(h, "mmd_ridge_load must be called before mmd_ridge_cv");
+    RidgeState& r = *h->ridge;
+    if (!alphas || !fold_bounds || !fold_scores_out || n_alphas < 1) return fail(h, "mmd_ridge_cv: bad arguments");
+    if (n_folds < 2 || n_folds > r.n)
+        return fail(h, "mmd_ridge_cv: k-fold cross-validation requires at least one train/test split by setting n_splits=2 or more "
+                       "and at most n_samples=%d, got n_splits=%d", r.n, n_folds);
+    if (fold_bounds[0] != 0 || fold_bounds[n_folds] != r.n) return fail(h, "mmd_ridge_cv: fold bounds must run from 0 to n");
+    for (int f = 0; f < n_folds; ++f)
+        if (fold_bounds[f + 1] <= fold_bounds[f]) return fail(h, "mmd_ridge_cv: empty fold %d", f);
+    CU(cudaSetDevice(h->device));
+    CU(r.count.ensure(sizeof(unsigned long long)));
+    int any_flag = 0;
+    for (int f = 0; f < n_folds; ++f) {
+        const int lo = fold_bounds[f], hi = fold_bounds[f + 1], n_val = hi - lo;
+        std::vector<int> tr, val;
+        for (int i = 0; i < r.n; ++i) (i >= lo && i < hi ? val : tr).push_back(i);
+        const int nvp = round_up(n_val, NB);
+        CU(r.yval.ensure((size_t)nvp * r.dp * sizeof(double)));
+        CU(r.dist.ensure((size_t)n_val * n_val * sizeof(double)));
+        CU(r.sq.ensure((size_t)2 * n_val * sizeof(double)));
+        for (int a = 0; a < n_alphas; ++a) {
+            int mp = 0;
+            span_begin(h, ST_SOLVE);
+            if (ridge_solve(h, r, tr, val, alphas[a], &mp)) return 1;
+            span_end(h, 0);
+            span_begin(h, ST_PREDICT);
+            if (ridge_predict_val(h, r, (int)tr.size(), n_val, mp)) return 1;
+            span_end(h, 0);
+            span_begin(h, ST_SCORE);
+            CU(launch_gather_block(r.Y.as<double>(), r.dp, r.idx_val.as<int>(), n_val, nullptr, r.dp, r.yval.as<double>(), nvp, r.dp,
+                                   0.0, 0.0, h->stream));
+            CU(launch_cosine_dist(r.pred.as<double>(), n_val, r.yval.as<double>(), n_val, r.d, r.dp, r.sq.as<double>(),
+                                  r.sq.as<double>() + n_val, r.dist.as<double>(), h->stream));
+            CU(launch_pairwise_count(r.dist.as<double>(), n_val, n_val, r.count.as<unsigned long long>(), h->stream));
+            span_end(h, 5);
+            unsigned long long count = 0;
+            int flag = 0;
+            CU(cudaMemcpyAsync(&count, r.count.p, sizeof(count), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaMemcpyAsync(&flag, r.flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+            any_flag |= flag;
+            const long den = (long)n_val * n_val - n_val;
+            fold_scores_out[(size_t)a * n_folds + f] = den > 0 ? (double)count / (double)den : std::nan("");
+        }
+    }
+    resolve_spans(h);
+    if (any_flag) return fail(h, "mmd_ridge_cv: a regularised Gram matrix was not positive definite");
+    return 0;
+}
+
+int mmd_ridge_fit(mmd_handle* h, double alpha, double* coef_out) {
+    if (!h) return 1;
+    if (!h->ridge || !h->ridge->loaded) return fail(h, "mmd_ridge_load must be called before mmd_ridge_fit");
+    RidgeState& r = *h->ridge;
+    CU(cudaSetDevice(h->device));
+    std::vector<int> tr(r.n), val;
+    for (int i = 0; i < r.n; ++i) tr[i] = i;
+    int mp = 0;
+    span_begin(h, ST_SOLVE);
+    if (ridge_solve(h, r, tr, val, alpha, &mp)) return 1;
+    CU(r.coef_t.ensure((size_t)r.dp * r.vp * sizeof(double)));
+    if (r.dual) {                                       // W^T = C^T X  (dp x vp)
+        DenseGemm g{};
+        g.A = r.rhs.as<double>(); g.lda = mp; g.B = r.Xt.as<double>(); g.ldb = r.np; g.C = r.coef_t.as<double>(); g.ldc = r.vp;
+        g.M = r.dp; g.N = r.vp; g.K = mp;               // mp == np: all trials
+        CU(launch_dense_gemm(g, h->stream));
+    } else {
+        CU(cudaMemcpyAsync(r.coef_t.p, r.rhs.p, (size_t)r.dp * r.vp * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    }
+    span_end(h, 1);
+    int flag = 0;
+    CU(cudaMemcpyAsync(&flag, r.flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (coef_out)                                       // sklearn's coef_ layout: (n_targets, n_features)
+        CU(cudaMemcpy2DAsync(coef_out, (size_t)r.v * sizeof(double), r.coef_t.p, (size_t)r.vp * sizeof(double),
+                             (size_t)r.v * sizeof(double), r.d, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    resolve_spans(h);
+    if (flag) return fail(h, "mmd_ridge_fit: the regularised Gram matrix is not positive definite");
+    r.fitted = true;
+    return 0;
+}
+
+int mmd_ridge_predict(mmd_handle* h, const void* X, int x_is_f32, int m, double* out) {
+    if (!h) return 1;
+    if (!h->ridge || !h->ridge->fitted) return fail(h, "mmd_ridge_fit must be called before mmd_ridge_predict");
+    if (!X || !out || m < 1) return fail(h, "mmd_ridge_predict: bad arguments");
+    RidgeState& r = *h->ridge;
+    CU(cudaSetDevice(h->device));
+    const int mpad = round_up(m, NB);
+    const size_t xb = (size_t)m * r.v * (x_is_f32 ? 4 : 8);
+    CU(r.stage.ensure(xb));
+    CU(r.kval.ensure((size_t)mpad * r.vp * sizeof(double)));
+    CU(r.pred_t.ensure((size_t)r.dp * mpad * sizeof(double)));
+    CU(r.pred.ensure((size_t)mpad * r.dp * sizeof(double)));
+    span_begin(h, ST_PREDICT);
+    CU(cudaMemcpyAsync(r.stage.p, X, xb, cudaMemcpyDefault, h->stream));
+    CU(launch_widen_pad(r.stage.p, x_is_f32, r.v, m, r.v, r.kval.as<double>(), mpad, r.vp, h->stream));
+    DenseGemm g{};
+    g.A = r.coef_t.as<double>(); g.lda = r.vp; g.B = r.kval.as<double>(); g.ldb = r.vp; g.C = r.pred_t.as<double>(); g.ldc = mpad;
+    g.M = r.dp; g.N = m; g.K = r.vp;
+    CU(launch_dense_gemm(g, h->stream));
+    CU(launch_transpose_f64(r.pred_t.as<double>(), mpad, r.dp, m, r.pred.as<double>(), r.dp, mpad, h->stream));
+    span_end(h, 3);
+    CU(cudaMemcpy2DAsync(out, (size_t)r.d * sizeof(double), r.pred.p, (size_t)r.dp * sizeof(double), (size_t)r.d * sizeof(double), m,
+                         cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    resolve_spans(h);
     return 0;
 }
 

@@ -484,24 +484,9 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
     const int s_p = task.s_p, jc = s_p / NB;
     const double* core = task.core_work;                        // rows 0..s_p-1: L11, rows s_p..: W1; stride s_p
     const long ldc = s_p;
-    if (jc > 0) {
-        // W1 -> the first s_p columns of this centre's W rows (the own panels extend them in place)
-        // eight independent 16-byte loads in flight per thread (the copy is latency bound otherwise)
-        const int n2 = s_p / 2, total = EVAL_PAD * n2;
-        for (int e0 = tid; e0 < total; e0 += THREADS * 8) {
-            double2 v[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const int e = e0 + q * THREADS;
-                if (e < total) v[q] = __ldg(reinterpret_cast<const double2*>(core + (long)(s_p + e / n2) * ldc + (e % n2) * 2));
-            }
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const int e = e0 + q * THREADS;
-                if (e < total) *reinterpret_cast<double2*>(M + (long)(kp + e / n2) * ld + (e % n2) * 2) = v[q];
-            }
-        }
-    }
+    // The group's W1 = E L11^{-T} (rows s_p.. of the core block) is read where it is needed -- as the leading K-range of the
+    // evaluation strips below and as the initial value of the backward solve -- and never copied into this centre's block.
+    const double* coreW = core + (long)s_p * ldc;
 
     // ---------------- factorisation + forward solve, panel by panel ----------------
     for (int j = 0; j < nblk; ++j) {
@@ -528,14 +513,28 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         const double* panel_rows = M + (long)K * ld;            // L[K..K+63][0..K)
         auto strip_row = [&](int u) { return u >= n_a ? kp + 16 * (u - n_a) : K + 16 * u; };   // first row in M
 
+        auto nop0 = [&]() {};
         for (int u0 = 0; u0 + NWARPS <= n_strips; u0 += NWARPS) {
             const int u = u0 + warp;
             const bool is_eval = u >= n_a;
             const int mrow = strip_row(u);
             Frag<8> acc;
-            auto a_row = [&](int r) -> const double* { return M + (long)(strip_row(u0 + (r >> 4)) + (r & 15)) * ld; };
             auto init = [&]() { strip_init<8>(acc, task, prm, is_eval, is_eval ? mrow - kp : mrow, K, lane); };
-            strip_gemm<false, 8>(acc, a_row, panel_rows, ld, K / KC, pipe, init, tid, lane, warp);
+            if (jc > 0) {
+                // columns [0, s_p): the evaluation rows come from the group's W1, the rows of A from this centre's L21
+                auto a_row1 = [&](int r) -> const double* {
+                    const int us = u0 + (r >> 4);
+                    return us >= n_a ? coreW + (long)(16 * (us - n_a) + (r & 15)) * ldc : M + (long)(strip_row(us) + (r & 15)) * ld;
+                };
+                strip_gemm<false, 8>(acc, a_row1, panel_rows, ld, s_p / KC, pipe, init, tid, lane, warp);
+                if (K > s_p) {
+                    auto a_row2 = [&](int r) -> const double* { return M + (long)(strip_row(u0 + (r >> 4)) + (r & 15)) * ld + s_p; };
+                    strip_gemm<false, 8>(acc, a_row2, panel_rows + s_p, ld, (K - s_p) / KC, pipe, nop0, tid, lane, warp);
+                }
+            } else {
+                auto a_row = [&](int r) -> const double* { return M + (long)(strip_row(u0 + (r >> 4)) + (r & 15)) * ld; };
+                strip_gemm<false, 8>(acc, a_row, panel_rows, ld, K / KC, pipe, init, tid, lane, warp);
+            }
             if (u0 == 0) {
                 // the four strips of the diagonal block: factor it, keep its inverse
                 const int fr = lane >> 2, fk = lane & 3;
@@ -559,9 +558,18 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         {   // split round: the last evaluation strip, 16 columns per warp
             const int mrow = strip_row(n_strips - 1);
             Frag<2> acc;
-            auto a_row = [&](int r) -> const double* { return r < 16 ? M + (long)(mrow + r) * ld : nullptr; };
             auto init = [&]() { strip_init<2>(acc, task, prm, true, mrow - kp, K + 16 * warp, lane); };
-            strip_gemm<false, 2>(acc, a_row, panel_rows, ld, K / KC, pipe, init, tid, lane, warp);
+            if (jc > 0) {
+                auto a_row1 = [&](int r) -> const double* { return r < 16 ? coreW + (long)(mrow - kp + r) * ldc : nullptr; };
+                strip_gemm<false, 2>(acc, a_row1, panel_rows, ld, s_p / KC, pipe, init, tid, lane, warp);
+                if (K > s_p) {
+                    auto a_row2 = [&](int r) -> const double* { return r < 16 ? M + (long)(mrow + r) * ld + s_p : nullptr; };
+                    strip_gemm<false, 2>(acc, a_row2, panel_rows + s_p, ld, (K - s_p) / KC, pipe, nop0, tid, lane, warp);
+                }
+            } else {
+                auto a_row = [&](int r) -> const double* { return r < 16 ? M + (long)(mrow + r) * ld : nullptr; };
+                strip_gemm<false, 2>(acc, a_row, panel_rows, ld, K / KC, pipe, init, tid, lane, warp);
+            }
             split_times_tri<false>(acc, Ism, pipe, lane, warp);
             strip_store<2>(acc, M + (long)mrow * ld + K + 16 * warp, ld, lane);
         }
@@ -589,7 +597,10 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         for (int u0 = 0; u0 + NWARPS <= N_ESTRIPS; u0 += NWARPS) {
             double* zrows = M + (long)(kp + 16 * (u0 + warp)) * ld;
             Frag<8> acc;
-            auto init = [&]() { strip_load_neg<8>(acc, zrows + c0, ld, lane); };
+            auto init = [&]() {
+                if (shared) strip_load_neg<8>(acc, coreW + (long)(16 * (u0 + warp)) * ldc + c0, ldc, lane);
+                else strip_load_neg<8>(acc, zrows + c0, ld, lane);
+            };
             if (Kb1 > 0) {
                 auto a_row1 = [&](int r) -> const double* { return M + (long)(kp + 16 * u0 + r) * ld + c0 + NB; };
                 strip_gemm<true, 8>(acc, a_row1, cpanel, ldc, Kb1 / KC, pipe, init, tid, lane, warp);
@@ -605,7 +616,10 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         {
             double* zrows = M + (long)(kp + 16 * (N_ESTRIPS - 1)) * ld;
             Frag<2> acc;
-            auto init = [&]() { strip_load_neg<2>(acc, zrows + c0 + 16 * warp, ld, lane); };
+            auto init = [&]() {
+                if (shared) strip_load_neg<2>(acc, coreW + (long)(16 * (N_ESTRIPS - 1)) * ldc + c0 + 16 * warp, ldc, lane);
+                else strip_load_neg<2>(acc, zrows + c0 + 16 * warp, ld, lane);
+            };
             if (Kb1 > 0) {
                 auto a_row1 = [&](int r) -> const double* { return r < 16 ? zrows + (long)r * ld + c0 + NB : nullptr; };
                 strip_gemm<true, 2>(acc, a_row1, cpanel, ldc, Kb1 / KC, pipe, init, tid, lane, warp);
@@ -624,7 +638,40 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
     if (tid == 0 && bad_pivot) prm.flags[task.centre] = 1;         // zeroed by the caller; sticky over the launches of a call
 }
 
+// One 64 x 64 diagonal block of the dense blocked Cholesky (dense.cu): same in-shared-memory factorisation as above.
+__global__ void __launch_bounds__(THREADS) chol_diag_kernel(double* A, long lda, double* linv, double* linvT, int* flag) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* Dsm = reinterpret_cast<double*>(smem_raw);
+    double* Ism = Dsm + NB * LDD;
+    __shared__ int bad_pivot;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) bad_pivot = 0;
+    for (int e = tid; e < NB * NB; e += THREADS) {
+        const int r = e / NB, c = e % NB;
+        Dsm[r * LDD + c] = A[(long)r * lda + c];
+        Ism[r * LDD + c] = 0.0;
+    }
+    __syncthreads();
+    factor_invert_block(Dsm, Ism, &bad_pivot, tid, lane, warp);
+    for (int e = tid; e < NB * NB; e += THREADS) {
+        const int r = e / NB, c = e % NB;
+        A[(long)r * lda + c] = c <= r ? Dsm[r * LDD + c] : 0.0;
+        const double v = c <= r ? Ism[r * LDD + c] : 0.0;
+        linv[r * NB + c] = v;
+        linvT[c * NB + r] = v;
+    }
+    if (tid == 0 && bad_pivot) *flag = 1;
+}
+
 }  // namespace
+
+cudaError_t launch_chol_diag(double* A, long lda, double* linv, double* linvT, int* flag, cudaStream_t s) {
+    const size_t smem = (size_t)2 * NB * LDD * sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    chol_diag_kernel<<<1, THREADS, smem, s>>>(A, lda, linv, linvT, flag);
+    return cudaGetLastError();
+}
 
 size_t factor_solve_smem_bytes() { return (size_t)(PIPE_DOUBLES + NB * LDD) * sizeof(double); }
 

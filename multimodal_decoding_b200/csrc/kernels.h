@@ -191,6 +191,33 @@ cudaError_t launch_rsub(const double* a, double* inout, long n, cudaStream_t s);
 cudaError_t launch_fold_latents(const __half* Yt, long ldy, int col0, int n_rows, int n_rows_pad, int Dp, double* cand, double* sq,
                                 cudaStream_t s);
 
+// ---- dense.cu (+ chol_diag_kernel in factor_solve.cu) ------------------------------------------------------------
+// float64 NT product on the DMMA pipe: C = A B^T (mode 0) or C -= A B^T (mode 1); K a multiple of 16, even leading dimensions
+struct DenseGemm {
+    const double* A;
+    long lda;
+    const double* B;
+    long ldb;
+    double* C;
+    long ldc;
+    int M, N, K;
+    int mode;
+    int lower_only;     // skip tiles strictly above the diagonal
+};
+cudaError_t launch_dense_gemm(const DenseGemm& p, cudaStream_t s);
+cudaError_t launch_gather_block(const double* in, long ld_in, const int* row_idx, int n_rows, const int* col_idx, int n_cols,
+                                double* out, int rows_out, int ld_out, double diag_add, double pad_diag, cudaStream_t s);
+cudaError_t launch_transpose_f64(const double* in, long ld_in, int n_rows_in, int n_cols_in, double* out, long ld_out, int rows_out,
+                                 cudaStream_t s);
+cudaError_t launch_widen_pad(const void* in, int is_f32, long ld_in, int n_rows, int n_cols, double* out, int rows_out, long ld_out,
+                             cudaStream_t s);
+// Cholesky factor of one 64 x 64 block (lower triangle of A read, L written back with zeros above the diagonal), its inverse
+// and the inverse's transpose (64 x 64 row-major each); *flag is set on a non-positive pivot
+cudaError_t launch_chol_diag(double* A, long lda, double* linv, double* linvT, int* flag, cudaStream_t s);
+cudaError_t dense_potrf(double* A, int np, double* linv, double* linvT, int* flag, cudaStream_t s);
+cudaError_t dense_potrs_t(const double* L, const double* Lt, const double* linv, const double* linvT, int np, double* Bt, int d,
+                          cudaStream_t s);
+
 // ---- prep.cu -----------------------------------------------------------------------------
 // task t reads its neighbour list adjacency[task_row_off[t] .. + task_k[t]) and writes kp_max-strided rows
 // task_core_off / task_core_n (optional): the task's shared core, an ascending list inside `adjacency`

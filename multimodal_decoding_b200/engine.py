@@ -201,6 +201,48 @@ class Engine:
                                                  len(fb) - 1, out.ctypes.data, flags.ctypes.data))
         return out, flags
 
+    # -- whole-brain ridge (ridge_regression_decoding.py:111-135) on the library's dense float64 kernels ------------
+    @staticmethod
+    def _dense(a):
+        """float32 / float64 C-contiguous numpy array (other dtypes are widened to float64) and its is_f32 flag."""
+        a = np.asarray(a)
+        if a.dtype not in (np.float32, np.float64):
+            a = a.astype(np.float64)
+        a = np.ascontiguousarray(a)
+        return a, int(a.dtype == np.float32)
+
+    def ridge_load(self, X, Y):
+        x, xf = self._dense(X)
+        y, yf = self._dense(Y)
+        if x.ndim != 2 or y.ndim != 2 or len(x) != len(y):
+            raise ValueError(f"X {x.shape} and Y {y.shape} must be 2-D with one row per trial")
+        self._check(self._lib.mmd_ridge_load(self._h, x.ctypes.data, xf, x.shape[0], x.shape[1], y.ctypes.data, yf, y.shape[1]))
+        self._ridge_shape = (x.shape[0], x.shape[1], y.shape[1])
+
+    def ridge_cv(self, alphas, fold_bounds):
+        """(n_alphas, n_folds) fold scores of the loaded problem (mmd_ridge_cv)."""
+        al = np.ascontiguousarray(np.asarray(alphas, dtype=np.float64))
+        fb = np.ascontiguousarray(np.asarray(fold_bounds, dtype=np.int32))
+        out = np.empty((len(al), len(fb) - 1), dtype=np.float64)
+        self._check(self._lib.mmd_ridge_cv(self._h, al.ctypes.data, len(al), fb.ctypes.data, len(fb) - 1, out.ctypes.data))
+        return out
+
+    def ridge_fit(self, alpha, want_coef=True):
+        """Refit on all trials; returns sklearn's coef_ (d x v) when asked."""
+        n, v, d = self._ridge_shape
+        coef = np.empty((d, v), dtype=np.float64) if want_coef else None
+        self._check(self._lib.mmd_ridge_fit(self._h, float(alpha), None if coef is None else coef.ctypes.data))
+        return coef
+
+    def ridge_predict(self, X):
+        x, xf = self._dense(X)
+        n, v, d = self._ridge_shape
+        if x.ndim != 2 or x.shape[1] != v:
+            raise ValueError(f"X has {x.shape[1] if x.ndim == 2 else '?'} features, but the ridge was fitted with {v}")
+        out = np.empty((x.shape[0], d), dtype=np.float64)
+        self._check(self._lib.mmd_ridge_predict(self._h, x.ctypes.data, xf, x.shape[0], out.ctypes.data))
+        return out
+
     def searchlight_null(self, adjacency, alpha, perm_test, perm_imagery):
         """Scores plus the null-distribution scores (searchlight.py:61-79) for target permutations given as index
         arrays into the test / imagery trials; returns (scores (n,8), flags (n,), null (n, n_perm, 6))."""

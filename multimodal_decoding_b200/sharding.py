@@ -71,3 +71,30 @@ def gather_scores(local_scores: np.ndarray, n_total: int) -> np.ndarray:
     dist.all_gather_into_tensor(everyone, mine)
     everyone = everyone.cpu().numpy().reshape(world, longest, width)
     return np.concatenate([everyone[r, : hi - lo] for r, (lo, hi) in enumerate(bounds)])
+
+
+def device_copy_via_peers(a: np.ndarray):
+    """(n x width) HOST array that every rank holds -> the same array as a CUDA tensor on this rank's GPU, moved by
+    all ranks together: rank r copies only its r-th block of rows over PCIe and the blocks are all-gathered over NVLink
+    (NCCL).  With N ranks the host-to-device traffic per rank falls to 1/N of the array.  Returns None when there is no NCCL
+    process group (the caller then hands the host array to the library, which copies all of it)."""
+    rank, world = _world()
+    if world == 1:
+        return None
+    import torch
+    import torch.distributed as dist
+    if dist.get_backend() != "nccl":
+        return None
+    a = np.asarray(a)
+    n, width = a.shape
+    bounds = split_bounds(n, world)
+    longest = max(hi - lo for lo, hi in bounds)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    lo, hi = bounds[rank]
+    mine = torch.zeros((longest, width), dtype=torch.from_numpy(a[:0]).dtype, device=dev)
+    mine[: hi - lo].copy_(torch.from_numpy(a[lo:hi]), non_blocking=True)
+    everyone = torch.empty((world * longest, width), dtype=mine.dtype, device=dev)
+    dist.all_gather_into_tensor(everyone, mine)
+    if all(b - a_ == longest for a_, b in bounds):
+        return everyone[:n]
+    return torch.cat([everyone[r * longest: r * longest + (b - a_)] for r, (a_, b) in enumerate(bounds)])
