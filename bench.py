@@ -419,6 +419,12 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
         s = (step * cps) % max(n_rows - cps + 1, 1)
         return A[s:s + cps]
 
+    A32 = A.astype(np.int32)                                    # the C ABI's own index type (mmd_searchlight)
+
+    def rows32_of(step):
+        s = (step * cps) % max(n_rows - cps + 1, 1)
+        return A32[s:s + cps]
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -438,7 +444,7 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
     upload_stats = eng.stats()
     setup_s = time.perf_counter() - t_setup
     for s in range(W):
-        eng.searchlight(rows_of(s), 1.0)
+        eng.searchlight(rows32_of(s), 1.0)
     eng.reset_stats()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -446,7 +452,7 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
         ev0.record(stream)
         t0 = time.perf_counter()
         for s in range(W, W + K):
-            scores, flags = eng.searchlight(rows_of(s), 1.0)
+            scores, flags = eng.searchlight(rows32_of(s), 1.0)
             if world > 1 and not weak:
                 gather_scores(scores, cps * world)           # the path's one collective: (V_shard x 8) blocks
         ev1.record(stream)
