@@ -274,11 +274,24 @@ def reference_centres_per_sec(arm, A_rows, n_centres):
 # ----------------------------------------------------------------------------------------------------------
 # roofline bookkeeping
 # ----------------------------------------------------------------------------------------------------------
-# DRAM bytes per centre (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of a full batch,
-# divided by the batch's centres): profiles/r1_*_v6_details.csv, captured with tools/gpu_round.sh and
-# tools/gpu_capture_fs.sh at config 2.  factor_solve = the per-centre launch (23.6 MB) + the shared-core launch (1.7 MB).
-NCU_DRAM_BYTES_PER_CENTRE = {"factor_solve": 25.3e6, "predict": 2.22e6, "score": 1.32e6, "syrk": 0.09e6}
+# DRAM bytes per centre of the per-centre kernels: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture
+# of a full batch, divided by the batch's centres -- extracted from the .ncu-rep files by tools/ncu_traffic.py into
+# profiles/r2_traffic.json (capture file names and sha256 inside).  factor_solve = the per-centre launch + the shared-core launch.
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r2_traffic.json")
 FP64_TENSOR_PEAK_TFLOPS = 37.1      # DMMA m8n8k4, measured on this pool with tools/peak_probe.cu (profiles/r1_measured_peaks_fp64.log)
+
+
+def load_traffic():
+    if not os.path.exists(TRAFFIC_FILE):
+        return {}, None
+    with open(TRAFFIC_FILE) as f:
+        d = json.load(f)
+    k = d["kernels"]
+    per = {name: v["dram_bytes_per_centre"] for name, v in k.items()}
+    if "factor_solve_core" in per:
+        per["factor_solve"] = per.get("factor_solve", 0.0) + per.pop("factor_solve_core")
+    src = "profiles/r2_traffic.json <- " + ", ".join(f"{v['capture']} (sha256 {v['sha256'][:12]})" for v in k.values())
+    return per, src
 
 
 def load_peaks():
@@ -313,12 +326,12 @@ def roofline_entry(stats, n_centres, args, peaks):
     shares = {s: round(ms[s] / max(sum(ms[x] for x in per_centre), 1e-9), 4) for s in per_centre}
     n_batches = max(stats["batches"], 1)                             # every batch launches each per-centre kernel once
     config2 = (k, ntr, D) == (750, 4000, 1024)
-    traffic = (round(NCU_DRAM_BYTES_PER_CENTRE[top] * n_centres / n_batches) if config2 and top in NCU_DRAM_BYTES_PER_CENTRE
-               else None)
+    per_centre_bytes, traffic_src = load_traffic()
+    traffic = round(per_centre_bytes[top] * n_centres / n_batches) if config2 and top in per_centre_bytes else None
     out = {"kernel": top, "stage_ms": {s: round(ms[s], 3) for s in per_centre}, "stage_share": shares,
            "launches_of_kernel": n_batches, "avg_launch_ms": round(ms[top] / n_batches, 3),
-           "traffic_source": "ncu --set full of one full batch, bytes per centre x centres per launch "
-                             "(profiles/r1_*_v6_details.csv)" if traffic else None}
+           "traffic_source": (f"ncu --set full capture of one full batch: DRAM bytes per centre x centres per launch; {traffic_src}"
+                              if traffic else None)}
     if top in ("syrk", "factor_solve", "predict"):
         executed = (stats["syrk_flops"] if top == "syrk" else stats["solve_flops"] if top == "factor_solve"
                     else stage_flops_per_centre(top, k, ntr, 144, D) * n_centres)
@@ -493,7 +506,8 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
         n_e2e = V if A_full is not None else world * cps
         e2e = {"value": round(n_e2e * K / e2e_s, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(cps * (8 * 8 + 4)), "ms_per_step": round(e2e_s / K * 1e3, 2),
-               "api": "custom_search_light(X_host_f16, y_host_f16, Ridge(alpha=1), A_rows, ...)"}
+               "api": "custom_search_light(X_host_f16, y_host_f16, Ridge(alpha=1), A_rows, ...)",
+               "host_ms_last_call_rank0": {k_: round(v_, 1) for k_, v_ in sl.LAST_TIMING.items()}}
     else:
         Xh, Yh = X16.cpu().numpy(), Y16.cpu().numpy()
         del X16, Y16

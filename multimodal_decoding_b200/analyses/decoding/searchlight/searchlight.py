@@ -34,6 +34,18 @@ SEARCHLIGHT_PERMUTATION_TESTING_RESULTS_DIR = os.path.join(SEARCHLIGHT_OUT_DIR, 
 DERANGEMENTS_THREE_DIMS = [[1, 2, 0], [2, 0, 1]]      # searchlight.py:35
 
 _ENGINES: dict[int, Engine] = {}
+LAST_TIMING: dict[str, float] = {}      # host milliseconds of the phases of the last custom_search_light call (diagnostics)
+
+
+class _Phase:
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        self.t0 = time.perf_counter()
+
+    def __exit__(self, *exc):
+        LAST_TIMING[self.name] = LAST_TIMING.get(self.name, 0.0) + (time.perf_counter() - self.t0) * 1e3
 
 
 def get_engine(device: int | None = None) -> Engine:
@@ -220,19 +232,23 @@ def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *,
         if is_caption is None:
             is_caption = _is_caption_mask(len(test_ids))
         # a rank of a vertex-sharded call stages the cross-covariance rows of its own neighbourhoods only
-        active = _active_vertices(A, np.shape(X)[1]) if shard_only and len(A) else None
+        with _Phase("active_vertices"):
+            active = _active_vertices(A, np.shape(X)[1]) if shard_only and len(A) else None
         Xd = _as_f16(X, "X")
         if shard_only and isinstance(Xd, np.ndarray):
             # every rank holds the same host X: each copies 1/N of its rows over PCIe, NVLink carries the rest
             from ....sharding import device_copy_via_peers
-            Xpeer = device_copy_via_peers(Xd)
+            with _Phase("x_via_peers"):
+                Xpeer = device_copy_via_peers(Xd)
             Xd = Xd if Xpeer is None else Xpeer
-        eng.upload(Xd, _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption, active_vertices=active)
-    if grid:
-        return search_light_cv(eng, A, grid[0], grid[1], len(train_ids))[:2]
-    if _is_ragged(A):
-        return eng.searchlight_ragged(A, alpha, anchors)
-    return eng.searchlight(A, alpha)
+        with _Phase("upload"):
+            eng.upload(Xd, _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption, active_vertices=active)
+    with _Phase("searchlight"):
+        if grid:
+            return search_light_cv(eng, A, grid[0], grid[1], len(train_ids))[:2]
+        if _is_ragged(A):
+            return eng.searchlight_ragged(A, alpha, anchors)
+        return eng.searchlight(A, alpha)
 
 
 def train_and_test(estimator, X, y=None, *, train_ids, test_ids, imagery_ids, null_distr_dir=None,
@@ -281,6 +297,8 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
     GPU even inside a process group (one whole searchlight per GPU, SURVEY.md §8e / BASELINE.json configs[4]).
     """
     from ....sharding import gather_scores, shard_range
+    LAST_TIMING.clear()
+    t_call = time.perf_counter()
     A = _rectangular(A)
     local_only = n_jobs == 1
     lo, hi = (0, len(A)) if local_only else shard_range(len(A))
@@ -299,7 +317,13 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
     if verbose:
         print(f"searchlight: centres {lo}..{hi} done on device {get_engine().device}, "
               f"{int(flags.sum())} not positive definite")
-    return _scores_to_dicts(scores if local_only else gather_scores(scores, len(A)))
+    if not local_only:
+        with _Phase("gather_scores"):
+            scores = gather_scores(scores, len(A))
+    with _Phase("score_dicts"):
+        out = _scores_to_dicts(scores)
+    LAST_TIMING["total"] = (time.perf_counter() - t_call) * 1e3
+    return out
 
 
 def get_adjacency_matrix(hemi, resolution, nan_locations=None, radius=None, num_neighbors=None):
