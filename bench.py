@@ -495,19 +495,25 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
 
         for s in range(min(W, 3)):
             e2e_step(s)
+        eng.reset_stats()
         barrier()
         t0 = time.perf_counter()
         for s in range(W, W + K):
             out = e2e_step(s)
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
+        e2e_stats = eng.stats()
         assert len(out) == (cps if weak else (V if A_full is not None else world * cps)) and len(out[0]) == 8
         h2d = Xh.nbytes + Yh.nbytes + cps * k * 4
         n_e2e = V if A_full is not None else world * cps
         e2e = {"value": round(n_e2e * K / e2e_s, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(cps * (8 * 8 + 4)), "ms_per_step": round(e2e_s / K * 1e3, 2),
                "api": "custom_search_light(X_host_f16, y_host_f16, Ridge(alpha=1), A_rows, ...)",
-               "host_ms_last_call_rank0": {k_: round(v_, 1) for k_, v_ in sl.LAST_TIMING.items()}}
+               "host_ms_last_call_rank0": {k_: round(v_, 1) for k_, v_ in sl.LAST_TIMING.items()},
+               "gpu_stage_ms_per_step_rank0": {k_: round(v_ / K, 1) for k_, v_ in e2e_stats["stage_ms"].items() if v_ > 0},
+               "plan_cache_hits": int(e2e_stats["plan_cache_hits"]),
+               "host_plan_ms_per_step": round(e2e_stats["host_plan_ms"] / K, 1),
+               "host_adjacency_ms_per_step": round(e2e_stats["host_adjacency_h2d_ms"] / K, 1)}
     else:
         Xh, Yh = X16.cpu().numpy(), Y16.cpu().numpy()
         del X16, Y16

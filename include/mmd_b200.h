@@ -143,6 +143,12 @@ int mmd_searchlight_ragged(mmd_handle* h, const int32_t* indices, const int64_t*
 int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
                          const int32_t* perm_test, const int32_t* perm_imagery, int n_perm, double* scores_out,
                          int32_t* flags_out, double* null_out);
+/* The same with one imagery permutation per CENTRE and permutation, as the reference draws them (searchlight.py:65 runs inside
+ * the per-centre train_and_test): perm_imagery_centre is (n_centres x n_perm x n_imagery) int32, HOST, indexed by the centre's
+ * row in `adjacency`; NULL = the shared table perm_imagery of mmd_searchlight_null. */
+int mmd_searchlight_null_pc(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
+                            const int32_t* perm_test, const int32_t* perm_imagery, const int32_t* perm_imagery_centre, int n_perm,
+                            double* scores_out, int32_t* flags_out, double* null_out);
 
 /* Alpha grid x K-fold cross-validation per neighbourhood: what
  *   GridSearchCV(Ridge(fit_intercept=False), param_grid=dict(alpha=alphas), scoring=make_scorer(pairwise_accuracy), cv=n_folds)

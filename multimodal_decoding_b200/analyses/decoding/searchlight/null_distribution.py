@@ -20,23 +20,27 @@ NULL_KEYS = ("pairwise_acc_captions", "pairwise_acc_images", "pairwise_acc_image
              "pairwise_acc_imagery_whole_test_set_no_std")    # dict order of searchlight.py:67-76
 
 
-def draw_imagery_permutations(n_permutations: int, n_imagery: int) -> np.ndarray:
-    """One derangement of the imagery targets per permutation, drawn like searchlight.py:65 from numpy's global
-    generator (seed `np.random.seed` for reproducible runs; the reference draws afresh for every centre, here the
-    draw is shared by all centres of a call)."""
+def draw_imagery_permutations(n_permutations: int, n_imagery: int, n_centres: int | None = None, seed=None) -> np.ndarray:
+    """Derangements of the imagery targets, drawn like searchlight.py:65: one per centre and permutation (the reference
+    draws inside the per-centre `train_and_test`), shape (n_centres, n_permutations, 3); `n_centres=None` gives one shared
+    (n_permutations, 3) table.  `seed=None` uses numpy's global generator like the reference (`np.random.seed` makes a run
+    reproducible); an integer seed draws from its own `RandomState`."""
     if n_imagery != 3:
         raise ValueError(f"the reference only defines imagery derangements for 3 trials (searchlight.py:35); got {n_imagery}")
-    return np.asarray([DERANGEMENTS_THREE_DIMS[np.random.choice(len(DERANGEMENTS_THREE_DIMS))]
-                       for _ in range(n_permutations)], dtype=np.int32)
+    rng = np.random if seed is None else np.random.RandomState(seed)
+    shape = (n_permutations,) if n_centres is None else (n_centres, n_permutations)
+    choice = rng.choice(len(DERANGEMENTS_THREE_DIMS), size=shape)
+    return np.asarray(DERANGEMENTS_THREE_DIMS, dtype=np.int32)[choice]
 
 
-def null_scores(eng, A, alpha, shuffled_indices, imagery_permutations=None, n_imagery=3):
-    """(scores (n,8), flags (n,), null (n, n_perm, 6)) for the centres in `A` on the engine's uploaded trials."""
+def null_scores(eng, A, alpha, shuffled_indices, imagery_permutations=None, n_imagery=3, seed=None):
+    """(scores (n,8), flags (n,), null (n, n_perm, 6)) for the centres in `A` on the engine's uploaded trials.
+    Without `imagery_permutations` every centre gets its own draws (reference semantics); `seed` makes them reproducible."""
     perm_test = np.asarray(shuffled_indices, dtype=np.int32)
     if perm_test.ndim != 2:
         raise ValueError("shuffled_indices must be a list of equally long index arrays (data.py:540-551)")
     if imagery_permutations is None:
-        imagery_permutations = draw_imagery_permutations(len(perm_test), n_imagery)
+        imagery_permutations = draw_imagery_permutations(len(perm_test), n_imagery, n_centres=len(A), seed=seed)
     return eng.searchlight_null(A, alpha, perm_test, imagery_permutations)
 
 

@@ -182,6 +182,8 @@ struct mmd_handle {
     cudaEvent_t up_copied = nullptr;        // recorded behind the last host-to-device copy of mmd_upload
     PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
     DevBuf st_in, st_edges, st_label, st_count, st_out;     // group-level statistics
+    DevBuf perm_im_centre;          // optional per-centre imagery permutations of the current mmd_searchlight_null_pc call
+    bool use_perm_im_centre = false;
     DevBuf dist, null_out, perm_test, perm_im, pa_pred, pa_lat, pa_dist, pa_sq, pa_count;
     // integer prediction GEMM (predict_i8.cu): digit planes of XtY (per upload) and of every centre's Zt (per batch),
     // their scales, the score kernel's tolerance input, the list of centres handed back to the float64 kernels
@@ -854,6 +856,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
         np.dist = h->dist.as<double>();
         np.perm_test = h->perm_test.as<int>();
         np.perm_imagery = h->perm_im.as<int>();
+        np.perm_imagery_centre = h->use_perm_im_centre ? h->perm_im_centre.as<int>() : nullptr;
         np.n_perm = h->n_perm;
         np.n_cap = h->n_cap;
         np.n_img = h->n_img;
@@ -1140,7 +1143,7 @@ std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
     return {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
                       &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
-                      &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->pa_pred, &h->pa_lat, &h->pa_dist,
+                      &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->perm_im_centre, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval,
                       &h->xplanes, &h->sX, &h->colmax, &h->zplanes, &h->sZ, &h->amp2, &h->i8_status, &h->reroute_list,
                       &h->reroute_counts, &h->margins, &h->active};
@@ -1666,13 +1669,22 @@ int mmd_predict_centre(mmd_handle* h, const int32_t* neighbours, int k, double a
                          (size_t)h->D * sizeof(double), n_eval, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     resolve_spans(h);
+    release_upload_staging(h);
     return 0;
 }
 
 int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
                          const int32_t* perm_test, const int32_t* perm_imagery, int n_perm, double* scores_out,
                          int32_t* flags_out, double* null_out) {
+    return mmd_searchlight_null_pc(h, adjacency, n_centres, k, alpha, perm_test, perm_imagery, nullptr, n_perm, scores_out,
+                                   flags_out, null_out);
+}
+
+int mmd_searchlight_null_pc(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
+                            const int32_t* perm_test, const int32_t* perm_imagery, const int32_t* perm_imagery_centre, int n_perm,
+                            double* scores_out, int32_t* flags_out, double* null_out) {
     if (!h) return 1;
+    if (perm_imagery_centre && !perm_imagery) perm_imagery = perm_imagery_centre;      // any valid table for the shared slot
     if (!adjacency || !scores_out || !perm_test || !null_out || (h->n_im > 0 && !perm_imagery))
         return fail(h, "mmd_searchlight_null: null pointer");
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight_null");
@@ -1694,8 +1706,19 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
         CU(cudaStreamSynchronize(h->stream));          // `internal` is pageable and goes out of scope
     }
     if (to_device(h, h->perm_im, perm_imagery, (size_t)n_perm * h->n_im)) return 1;
+    h->use_perm_im_centre = false;
+    if (perm_imagery_centre && h->n_im > 0) {
+        const size_t n_pc = (size_t)n_centres * n_perm * h->n_im;
+        for (size_t i = 0; i < n_pc; ++i)
+            if (perm_imagery_centre[i] < 0 || perm_imagery_centre[i] >= h->n_im)
+                return fail(h, "mmd_searchlight_null: imagery permutation index out of range");
+        if (to_device(h, h->perm_im_centre, perm_imagery_centre, n_pc)) return 1;
+        h->use_perm_im_centre = true;
+    }
     const Rows rows{adjacency, nullptr, k, nullptr, n_centres};
-    if (run_searchlight(h, rows, alpha, true)) {
+    const int rc_null = run_searchlight(h, rows, alpha, true);
+    h->use_perm_im_centre = false;
+    if (rc_null) {
         cudaStreamSynchronize(h->stream);
         h->spans.clear();
         h->events_used = 0;

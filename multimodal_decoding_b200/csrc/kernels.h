@@ -156,6 +156,8 @@ struct NullParams {
     const double* dist;        // as written by the score kernel
     const int* perm_test;      // (n_perm x n_test) candidate column playing the role of test row g's own latent
     const int* perm_imagery;   // (n_perm x n_im)   imagery candidate (0..n_im-1) playing the role of imagery row i's latent
+    const int* perm_imagery_centre;   // optional (n_centres x n_perm x n_im), indexed by task.centre: one draw per centre and
+                                      // permutation like searchlight.py:65; overrides perm_imagery
     int n_perm, n_cap, n_img, n_im;
     double* null_out;          // (n_centres x n_perm x 6), written at row task.centre
 };

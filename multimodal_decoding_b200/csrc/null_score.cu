@@ -35,7 +35,8 @@ __global__ void __launch_bounds__(NULL_THREADS) null_score_kernel(NullParams prm
     for (int w = threadIdx.x; w < n_perm * rows_per_perm; w += blockDim.x) {
         const int p = w / rows_per_perm, rr = w % rows_per_perm;
         const int* pt = prm.perm_test + (long)p * n_test;
-        const int* pi = prm.perm_imagery + (long)p * n_im;
+        const int* pi = prm.perm_imagery_centre ? prm.perm_imagery_centre + ((long)task.centre * n_perm + p) * n_im
+                                                : prm.perm_imagery + (long)p * n_im;
         if (rr < n_test) {
             const bool cap = rr < n_cap;
             const double* row = Dt + rr;                     // row[x * LDR] = d(rr, x)

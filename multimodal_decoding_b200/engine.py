@@ -245,22 +245,27 @@ class Engine:
 
     def searchlight_null(self, adjacency, alpha, perm_test, perm_imagery):
         """Scores plus the null-distribution scores (searchlight.py:61-79) for target permutations given as index
-        arrays into the test / imagery trials; returns (scores (n,8), flags (n,), null (n, n_perm, 6))."""
+        arrays into the test / imagery trials; returns (scores (n,8), flags (n,), null (n, n_perm, 6)).
+        `perm_imagery`: (n_perm, n_imagery) shared by all centres, or (n_centres, n_perm, n_imagery) -- one draw per centre
+        and permutation like the reference (mmd_searchlight_null_pc)."""
         adj = np.ascontiguousarray(np.asarray(adjacency, dtype=np.int32))
         if adj.ndim != 2:
             raise ValueError("adjacency must be rectangular (n_centres, k); ragged radius mode is not supported")
         pt = np.ascontiguousarray(np.asarray(perm_test, dtype=np.int32))
         pi = np.ascontiguousarray(np.asarray(perm_imagery, dtype=np.int32))
-        if pt.ndim != 2 or pi.ndim != 2 or len(pt) != len(pi):
-            raise ValueError("perm_test (n_perm, n_test) and perm_imagery (n_perm, n_imagery) must have one row per permutation")
         n, k = adj.shape
+        per_centre = pi.ndim == 3
+        if pt.ndim != 2 or pi.ndim not in (2, 3) or pi.shape[-2] != len(pt) or (per_centre and len(pi) != n):
+            raise ValueError("perm_test (n_perm, n_test) and perm_imagery (n_perm, n_imagery) or (n_centres, n_perm, n_imagery) "
+                             "must have one row per permutation")
         n_perm = len(pt)
         scores = np.empty((n, _lib.N_SCORES), dtype=np.float64)
         flags = np.zeros(n, dtype=np.int32)
         null = np.empty((n, n_perm, _lib.N_NULL_SCORES), dtype=np.float64)
-        self._check(self._lib.mmd_searchlight_null(self._h, adj.ctypes.data, n, k, float(alpha), pt.ctypes.data,
-                                                   pi.ctypes.data, n_perm, scores.ctypes.data, flags.ctypes.data,
-                                                   null.ctypes.data))
+        shared = np.ascontiguousarray(pi[0]) if per_centre else pi
+        self._check(self._lib.mmd_searchlight_null_pc(self._h, adj.ctypes.data, n, k, float(alpha), pt.ctypes.data,
+                                                      shared.ctypes.data, pi.ctypes.data if per_centre else None, n_perm,
+                                                      scores.ctypes.data, flags.ctypes.data, null.ctypes.data))
         return scores, flags, null
 
     # -- eval.py primitives (arbitrary shapes, float64) -----------------------------------------

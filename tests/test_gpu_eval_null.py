@@ -77,6 +77,13 @@ def test_null_distribution_matches_reference(golden_dir, tmp_path):
         scores, flags, null = eng.searchlight_null(g["adjacency"][[c]], 1.0, g["perms"], im_perm)
         assert flags.sum() == 0
         assert np.array_equal(null[0], g["null_scores"][ci])
+    # all centres in one call, every centre with the draws the reference made for it (mmd_searchlight_null_pc)
+    per_centre = np.stack([g["derangements"][g["derangement_choice"][ci]] for ci in range(len(g["centres"]))])
+    scores, flags, null = eng.searchlight_null(g["adjacency"][g["centres"]], 1.0, g["perms"], per_centre)
+    assert flags.sum() == 0 and np.array_equal(null, g["null_scores"])
+    a = nd.draw_imagery_permutations(5, 3, n_centres=4, seed=7)
+    assert a.shape == (4, 5, 3) and np.array_equal(a, nd.draw_imagery_permutations(5, 3, n_centres=4, seed=7))
+    assert {tuple(r) for r in a.reshape(-1, 3)} <= {(1, 2, 0), (2, 0, 1)} and nd.draw_imagery_permutations(5, 3).shape == (5, 3)
     # the drop-in writes the reference's per-centre pickles
     np.random.seed(1234)
     out = sl.custom_group_iter_search_light([g["adjacency"][c] for c in g["centres"]], list(g["centres"]),
