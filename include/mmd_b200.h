@@ -149,6 +149,11 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
 int mmd_searchlight_null_pc(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
                             const int32_t* perm_test, const int32_t* perm_imagery, const int32_t* perm_imagery_centre, int n_perm,
                             double* scores_out, int32_t* flags_out, double* null_out);
+/* ... and for ragged (radius-mode) neighbourhoods, arguments as mmd_searchlight_ragged (searchlight.py:61-79 with :164-171). */
+int mmd_searchlight_null_ragged(mmd_handle* h, const int32_t* indices, const int64_t* offsets, const int32_t* anchors, int n_centres,
+                                double alpha, const int32_t* perm_test, const int32_t* perm_imagery,
+                                const int32_t* perm_imagery_centre, int n_perm, double* scores_out, int32_t* flags_out,
+                                double* null_out);
 
 /* Alpha grid x K-fold cross-validation per neighbourhood: what
  *   GridSearchCV(Ridge(fit_intercept=False), param_grid=dict(alpha=alphas), scoring=make_scorer(pairwise_accuracy), cv=n_folds)

@@ -15,7 +15,7 @@ EVAL_PAD = 144
 EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload", "mmd_upload_active", "mmd_mark_vertices",
     "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
-    "mmd_searchlight_null", "mmd_searchlight_null_pc", "mmd_searchlight_cv", "mmd_ridge_load", "mmd_ridge_cv", "mmd_ridge_fit", "mmd_ridge_predict", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
+    "mmd_searchlight_null", "mmd_searchlight_null_pc", "mmd_searchlight_null_ragged", "mmd_searchlight_cv", "mmd_ridge_load", "mmd_ridge_cv", "mmd_ridge_fit", "mmd_ridge_predict", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
     "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels", "mmd_check_guards", "mmd_guard_selftest",
     "mmd_set_predict_mode", "mmd_enable_margins", "mmd_get_margins",
 ]
@@ -71,6 +71,8 @@ def load():
     lib.mmd_searchlight_null.restype = i32
     lib.mmd_searchlight_null_pc.argtypes = [vp, vp, i32, i32, dbl, vp, vp, vp, i32, vp, vp, vp]
     lib.mmd_searchlight_null_pc.restype = i32
+    lib.mmd_searchlight_null_ragged.argtypes = [vp, vp, vp, vp, i32, dbl, vp, vp, vp, i32, vp, vp, vp]
+    lib.mmd_searchlight_null_ragged.restype = i32
     lib.mmd_searchlight_cv.argtypes = [vp, vp, i32, i32, vp, i32, vp, i32, vp, vp]
     lib.mmd_searchlight_cv.restype = i32
     lib.mmd_ridge_load.argtypes = [vp, vp, i32, i32, i32, vp, i32, i32]

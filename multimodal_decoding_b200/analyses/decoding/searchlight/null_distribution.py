@@ -41,7 +41,7 @@ def null_scores(eng, A, alpha, shuffled_indices, imagery_permutations=None, n_im
         raise ValueError("shuffled_indices must be a list of equally long index arrays (data.py:540-551)")
     if imagery_permutations is None:
         imagery_permutations = draw_imagery_permutations(len(perm_test), n_imagery, n_centres=len(A), seed=seed)
-    return eng.searchlight_null(A, alpha, perm_test, imagery_permutations)
+    return eng.searchlight_null(A, alpha, perm_test, imagery_permutations)      # rectangular or ragged neighbourhoods
 
 
 def null_array_to_dicts(null_row: np.ndarray) -> list:

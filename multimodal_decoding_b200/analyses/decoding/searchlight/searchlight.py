@@ -34,6 +34,8 @@ SEARCHLIGHT_PERMUTATION_TESTING_RESULTS_DIR = os.path.join(SEARCHLIGHT_OUT_DIR, 
 DERANGEMENTS_THREE_DIMS = [[1, 2, 0], [2, 0, 1]]      # searchlight.py:35
 
 _ENGINES: dict[int, Engine] = {}
+NUM_CV_SPLITS = 5                       # ridge_regression_decoding.py:20
+LAST_CV: dict = {}                      # best_alpha / mean_test_score of the last cross-validated call (this rank's centres)
 LAST_TIMING: dict[str, float] = {}      # host milliseconds of the phases of the last custom_search_light call (diagnostics)
 
 
@@ -245,7 +247,10 @@ def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *,
             eng.upload(Xd, _as_f16(y, "y"), train_ids, test_ids, imagery_ids, is_caption, active_vertices=active)
     with _Phase("searchlight"):
         if grid:
-            return search_light_cv(eng, A, grid[0], grid[1], len(train_ids))[:2]
+            scores, flags, best_alpha, mean = search_light_cv(eng, A, grid[0], grid[1], len(train_ids))
+            LAST_CV.clear()
+            LAST_CV.update(best_alpha=best_alpha, mean_test_score=mean, alphas=list(grid[0]), n_splits=grid[1])
+            return scores, flags
         if _is_ragged(A):
             return eng.searchlight_ragged(A, alpha, anchors)
         return eng.searchlight(A, alpha)
@@ -281,8 +286,7 @@ def custom_group_iter_search_light(list_rows, list_indices, estimator, X, y, tra
     else:
         eng = get_engine()
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
-        scores, _ = _null_branch(eng, _require_rectangular(_rectangular(list_rows), "the null-distribution branch"),
-                                 list_indices, _estimator_alpha(estimator),
+        scores, _ = _null_branch(eng, _rectangular(list_rows), list_indices, _estimator_alpha(estimator),
                                  len(imagery_ids), null_distr_dir, shuffled_indices)
     return list(_scores_to_dicts(scores))
 
@@ -308,7 +312,6 @@ def custom_search_light(X, y, estimator, A, train_ids, test_ids, imagery_ids, n_
         scores, flags = search_light_scores(X, y, estimator, A[lo:hi], train_ids, test_ids, imagery_ids,
                                             anchors=anchors, shard_only=(hi - lo) < len(A))
     else:
-        _require_rectangular(A, "the null-distribution branch")
         eng = get_engine()
         eng.upload(_as_f16(X, "X"), _as_f16(y, "y"), train_ids, test_ids, imagery_ids, _is_caption_mask(len(test_ids)))
         scores, flags = _null_branch(eng, A[lo:hi], np.arange(lo, hi), _estimator_alpha(estimator), len(imagery_ids),
@@ -416,6 +419,12 @@ def run(args):
                 )
 
                 model = Ridge(alpha=args.l2_regularization_alpha, fit_intercept=False)
+                if args.l2_regularization_alphas:
+                    # north star: a cross-validated ridge per vertex -- the GridSearchCV construction of
+                    # ridge_regression_decoding.py:111-117 applied to every neighbourhood (mmd_searchlight_cv)
+                    from sklearn.model_selection import GridSearchCV
+                    model = GridSearchCV(estimator=Ridge(fit_intercept=False),
+                                         param_grid=dict(alpha=list(args.l2_regularization_alphas)), cv=NUM_CV_SPLITS)
 
                 null_distr_dir = None
                 if args.create_null_distr:
@@ -445,9 +454,12 @@ def run(args):
                     "distances": distances,
                     "scores": scores,
                 }
+                if args.l2_regularization_alphas and len(LAST_CV.get("best_alpha", ())) == len(scores):
+                    results_dict["best_alpha"] = LAST_CV["best_alpha"]
+                    results_dict["mean_test_score"] = LAST_CV["mean_test_score"]
                 results_file_path = get_results_file_path(
                     feats_config, hemi, subject, training_mode, args.resolution, searchlight_mode_from_args(args),
-                    args.l2_regularization_alpha
+                    "cv" if args.l2_regularization_alphas else args.l2_regularization_alpha
                 )
                 pickle.dump(results_dict, open(results_file_path, 'wb'))
 
@@ -490,6 +502,9 @@ def get_args(argv=None):
     parser.add_argument("--resolution", type=str, default=DEFAULT_RESOLUTION)
     parser.add_argument("--hemis", type=str, nargs="+", default=["left", "right"])
     parser.add_argument("--l2-regularization-alpha", type=float, default=1)
+    # not in the reference's searchlight CLI: an alpha grid switches on 5-fold cross-validation per vertex (the flag of
+    # ridge_regression_decoding.py:36); results go to alpha_cv.p with the selected alpha per vertex beside the scores
+    parser.add_argument("--l2-regularization-alphas", type=float, nargs='+', default=None)
     parser.add_argument("--radius", type=float, default=None)
     parser.add_argument("--n-neighbors", type=int, default=None)
     parser.add_argument("--n-jobs", type=int, default=DEFAULT_N_JOBS)

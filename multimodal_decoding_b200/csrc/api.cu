@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <future>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -180,6 +181,10 @@ struct mmd_handle {
     int n_active = 0;                       // 0 = all vertices
     DevBuf up_x, up_y, up_train, up_eval;   // mmd_upload's staging copies: alive until the packing kernels have run
     cudaEvent_t up_copied = nullptr;        // recorded behind the last host-to-device copy of mmd_upload
+    PinnedBuf batch_host[2];        // per-batch task arrays, packed: pinned and double-buffered so that the one copy per
+    cudaEvent_t batch_copied[2] = {nullptr, nullptr};      // batch is truly asynchronous (a pageable source may make
+    int batch_half = 0;             // cudaMemcpyAsync wait for the stream first)
+    DevBuf batch_dev;
     PinnedBuf adj_host;             // int32 staging copy of the caller's adjacency: async H2D overlaps the host grouping
     DevBuf st_in, st_edges, st_label, st_count, st_out;     // group-level statistics
     DevBuf perm_im_centre;          // optional per-centre imagery permutations of the current mmd_searchlight_null_pc call
@@ -326,6 +331,19 @@ struct PlanCache {
     Clustering cl;
     std::vector<int> chunk_start;
     std::vector<Plan> plans;
+    // the unions and shared cores of every chunk are page-locked where they lie, so that their copies to the device are
+    // asynchronous (a pageable source makes cudaMemcpyAsync wait for the stream first: the GPU would idle at every chunk)
+    std::vector<void*> registered;
+    void pin(void* p, size_t bytes) {
+        if (p && bytes && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) registered.push_back(p);
+        else cudaGetLastError();
+    }
+    void unpin_all() {
+        for (void* p : registered) cudaHostUnregister(p);
+        registered.clear();
+        cudaGetLastError();
+    }
+    ~PlanCache() { unpin_all(); }
 };
 namespace {
 
@@ -719,28 +737,54 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     h->n_batches += 1;
     h->n_core_tasks += n_core;
     if (pool_doubles * sizeof(double) > h->gram_pool.bytes) return fail(h, "internal: gram pool too small");
-    if (to_device(h, h->task_row, task_row_off.data(), n_all)) return 1;
-    if (to_device(h, h->task_k, task_k.data(), n_all)) return 1;
-    if (to_device(h, h->task_union_off, task_un_off.data(), n_all)) return 1;
-    if (to_device(h, h->task_union_n, task_un_n.data(), n_all)) return 1;
-    if (to_device(h, h->task_core_off, task_core_off.data(), n_all)) return 1;
-    if (to_device(h, h->task_core_n, task_core_n.data(), n_all)) return 1;
-    if (to_device(h, h->tasks, tasks.data(), n_all)) return 1;
-    if (to_device(h, h->probs, probs.data(), n_cl)) return 1;
+    // one packed block per batch: pinned staging (double-buffered) -> one asynchronous copy
+    size_t blk = 0;
+    auto place = [&](size_t bytes) {
+        const size_t o = blk;
+        blk = (blk + bytes + 255) & ~(size_t)255;
+        return o;
+    };
+    const size_t o_row = place((size_t)n_all * sizeof(long)), o_k = place((size_t)n_all * sizeof(int)),
+                 o_unoff = place((size_t)n_all * sizeof(long)), o_unn = place((size_t)n_all * sizeof(int)),
+                 o_coff = place((size_t)n_all * sizeof(long)), o_cn = place((size_t)n_all * sizeof(int)),
+                 o_tasks = place((size_t)n_all * sizeof(CentreTask)), o_probs = place((size_t)n_cl * sizeof(GemmProblem));
+    const int half = h->batch_half;
+    h->batch_half ^= 1;
+    if (!h->batch_copied[half]) CU(cudaEventCreateWithFlags(&h->batch_copied[half], cudaEventDisableTiming));
+    else CU(cudaEventSynchronize(h->batch_copied[half]));                // the copy that last used this half has landed
+    CU(h->batch_host[half].ensure(blk));
+    CU(h->batch_dev.ensure(blk));
+    {
+        char* hp = static_cast<char*>(h->batch_host[half].p);
+        memcpy(hp + o_row, task_row_off.data(), (size_t)n_all * sizeof(long));
+        memcpy(hp + o_k, task_k.data(), (size_t)n_all * sizeof(int));
+        memcpy(hp + o_unoff, task_un_off.data(), (size_t)n_all * sizeof(long));
+        memcpy(hp + o_unn, task_un_n.data(), (size_t)n_all * sizeof(int));
+        memcpy(hp + o_coff, task_core_off.data(), (size_t)n_all * sizeof(long));
+        memcpy(hp + o_cn, task_core_n.data(), (size_t)n_all * sizeof(int));
+        memcpy(hp + o_tasks, tasks.data(), (size_t)n_all * sizeof(CentreTask));
+        memcpy(hp + o_probs, probs.data(), (size_t)n_cl * sizeof(GemmProblem));
+    }
+    CU(cudaMemcpyAsync(h->batch_dev.p, h->batch_host[half].p, blk, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaEventRecord(h->batch_copied[half], h->stream));
+    char* dp = static_cast<char*>(h->batch_dev.p);
+    const CentreTask* tasks_dev = reinterpret_cast<const CentreTask*>(dp + o_tasks);
+    const GemmProblem* probs_dev = reinterpret_cast<const GemmProblem*>(dp + o_probs);
 
     span_begin(h, ST_PREP);
-    CU(launch_prep_tasks(h->adj.as<int>(), h->task_row.as<long>(), h->task_k.as<int>(), k_max, kp,
-                         h->task_union_off.as<long>(), h->task_union_n.as<int>(), h->union_vertices.as<int>(),
-                         h->task_core_off.as<long>(), h->task_core_n.as<int>(), h->V,
+    CU(launch_prep_tasks(h->adj.as<int>(), reinterpret_cast<const long*>(dp + o_row), reinterpret_cast<const int*>(dp + o_k), k_max, kp,
+                         reinterpret_cast<const long*>(dp + o_unoff), reinterpret_cast<const int*>(dp + o_unn),
+                         h->union_vertices.as<int>(), reinterpret_cast<const long*>(dp + o_coff),
+                         reinterpret_cast<const int*>(dp + o_cn), h->V,
                          h->vertex_bad.as<unsigned char>(), n_all, h->nbr_sorted.as<int>(), h->loc.as<int>(), h->misc_flag.as<int>(), h->stream));
     span_end(h);
 
     span_begin(h, ST_SYRK);
-    CU(launch_gemm_gather(h->probs.as<GemmProblem>(), n_cl, max_u, max_u, h->stream));
+    CU(launch_gemm_gather(probs_dev, n_cl, max_u, max_u, h->stream));
     span_end(h);
 
     SolveParams sp{};
-    sp.tasks = h->tasks.as<CentreTask>();
+    sp.tasks = tasks_dev;
     sp.n_tasks = n_tasks;
     sp.kp_max = kp;
     sp.alpha = alpha;
@@ -1102,6 +1146,7 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
             acc += m;
         }
         pc.chunk_start.push_back(n_cl);
+        pc.unpin_all();
         pc.plans.assign(pc.chunk_start.size() - 1, Plan());
     }
     const Clustering& cl = pc.cl;
@@ -1110,8 +1155,19 @@ int run_searchlight(mmd_handle* h, const Rows& rows_in, double alpha, bool with_
     h->n_clusters += n_clusters;
     const int n_chunks = (int)chunk_start.size() - 1;
     const int group_size = h->group_size, V = h->V;
+    std::mutex pin_mutex;
+    const int device_id = h->device;
+    auto pin_plan = [&](int i) {
+        std::lock_guard<std::mutex> lock(pin_mutex);
+        cudaSetDevice(device_id);                          // planner threads start on device 0
+        Plan& pl = pc.plans[i];
+        pc.pin(pl.un_vert.data(), pl.un_vert.size() * sizeof(int));
+        pc.pin(pl.core_vert.data(), pl.core_vert.size() * sizeof(int));
+    };
     auto plan_chunk = [&, group_size, V, n_threads, hit](int i) {
-        if (!hit) build_plan(rows, V, cl, chunk_start[i], chunk_start[i + 1], group_size, n_threads, pc.plans[i]);
+        if (hit) return;
+        build_plan(rows, V, cl, chunk_start[i], chunk_start[i + 1], group_size, n_threads, pc.plans[i]);
+        pin_plan(i);
     };
     std::future<void> pending = std::async(std::launch::async, plan_chunk, 0);
     int rc = 0;
@@ -1146,7 +1202,7 @@ std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
                       &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->perm_im_centre, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval,
                       &h->xplanes, &h->sX, &h->colmax, &h->zplanes, &h->sZ, &h->amp2, &h->i8_status, &h->reroute_list,
-                      &h->reroute_counts, &h->margins, &h->active};
+                      &h->reroute_counts, &h->margins, &h->active, &h->batch_dev};
 }
 
 // the stream must have passed mmd_upload's kernels (any later synchronisation of h->stream will do)
@@ -1231,6 +1287,10 @@ void mmd_destroy(mmd_handle* h) {
     release_upload_staging(h);
     if (h->up_copied) cudaEventDestroy(h->up_copied);
     h->adj_host.release();
+    for (int i = 0; i < 2; ++i) {
+        h->batch_host[i].release();
+        if (h->batch_copied[i]) cudaEventDestroy(h->batch_copied[i]);
+    }
     delete h->plan_cache;
     if (h->ridge) {
         for (DevBuf* b : h->ridge->all()) b->release();
@@ -1680,12 +1740,12 @@ int mmd_searchlight_null(mmd_handle* h, const int32_t* adjacency, int n_centres,
                                    flags_out, null_out);
 }
 
-int mmd_searchlight_null_pc(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
-                            const int32_t* perm_test, const int32_t* perm_imagery, const int32_t* perm_imagery_centre, int n_perm,
-                            double* scores_out, int32_t* flags_out, double* null_out) {
-    if (!h) return 1;
+static int searchlight_null_rows(mmd_handle* h, const Rows& rows, double alpha, const int32_t* perm_test,
+                                 const int32_t* perm_imagery, const int32_t* perm_imagery_centre, int n_perm, double* scores_out,
+                                 int32_t* flags_out, double* null_out) {
+    const int n_centres = rows.n;
     if (perm_imagery_centre && !perm_imagery) perm_imagery = perm_imagery_centre;      // any valid table for the shared slot
-    if (!adjacency || !scores_out || !perm_test || !null_out || (h->n_im > 0 && !perm_imagery))
+    if (!rows.data || !scores_out || !perm_test || !null_out || (h->n_im > 0 && !perm_imagery))
         return fail(h, "mmd_searchlight_null: null pointer");
     if (!h->uploaded) return fail(h, "mmd_upload must be called before mmd_searchlight_null");
     if (n_centres < 0 || n_perm < 1 || n_perm > 1700) return fail(h, "mmd_searchlight_null: n_perm must be 1..1700 per call (split larger sets)");
@@ -1715,7 +1775,6 @@ int mmd_searchlight_null_pc(mmd_handle* h, const int32_t* adjacency, int n_centr
         if (to_device(h, h->perm_im_centre, perm_imagery_centre, n_pc)) return 1;
         h->use_perm_im_centre = true;
     }
-    const Rows rows{adjacency, nullptr, k, nullptr, n_centres};
     const int rc_null = run_searchlight(h, rows, alpha, true);
     h->use_perm_im_centre = false;
     if (rc_null) {
@@ -1735,6 +1794,31 @@ int mmd_searchlight_null_pc(mmd_handle* h, const int32_t* adjacency, int n_centr
     release_upload_staging(h);
     if (collect_i8_stats(h)) return 1;
     return report_input_flags(h, bad, y_bad, "mmd_searchlight_null");
+}
+
+int mmd_searchlight_null_pc(mmd_handle* h, const int32_t* adjacency, int n_centres, int k, double alpha,
+                            const int32_t* perm_test, const int32_t* perm_imagery, const int32_t* perm_imagery_centre, int n_perm,
+                            double* scores_out, int32_t* flags_out, double* null_out) {
+    if (!h) return 1;
+    const Rows rows{adjacency, nullptr, k, nullptr, n_centres};
+    return searchlight_null_rows(h, rows, alpha, perm_test, perm_imagery, perm_imagery_centre, n_perm, scores_out, flags_out, null_out);
+}
+
+int mmd_searchlight_null_ragged(mmd_handle* h, const int32_t* indices, const int64_t* offsets, const int32_t* anchors, int n_centres,
+                                double alpha, const int32_t* perm_test, const int32_t* perm_imagery,
+                                const int32_t* perm_imagery_centre, int n_perm, double* scores_out, int32_t* flags_out,
+                                double* null_out) {
+    if (!h) return 1;
+    if (!indices || !offsets) return fail(h, "mmd_searchlight_null_ragged: null pointer");
+    if (n_centres < 0) return fail(h, "mmd_searchlight_null_ragged: negative centre count");
+    if (n_centres > 0) {
+        if (offsets[0] != 0) return fail(h, "mmd_searchlight_null_ragged: offsets[0] must be 0");
+        for (int i = 0; i < n_centres; ++i)
+            if (offsets[i + 1] <= offsets[i])
+                return fail(h, "mmd_searchlight_null_ragged: centre %d has an empty neighbourhood or offsets decrease", i);
+    }
+    const Rows rows{indices, offsets, 0, anchors, n_centres};
+    return searchlight_null_rows(h, rows, alpha, perm_test, perm_imagery, perm_imagery_centre, n_perm, scores_out, flags_out, null_out);
 }
 
 // GridSearchCV semantics per neighbourhood (ridge_regression_decoding.py:111-117; KFold without shuffling:

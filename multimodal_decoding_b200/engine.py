@@ -243,17 +243,26 @@ class Engine:
         self._check(self._lib.mmd_ridge_predict(self._h, x.ctypes.data, xf, x.shape[0], out.ctypes.data))
         return out
 
-    def searchlight_null(self, adjacency, alpha, perm_test, perm_imagery):
+    def searchlight_null(self, adjacency, alpha, perm_test, perm_imagery, anchors=None):
         """Scores plus the null-distribution scores (searchlight.py:61-79) for target permutations given as index
         arrays into the test / imagery trials; returns (scores (n,8), flags (n,), null (n, n_perm, 6)).
         `perm_imagery`: (n_perm, n_imagery) shared by all centres, or (n_centres, n_perm, n_imagery) -- one draw per centre
-        and permutation like the reference (mmd_searchlight_null_pc)."""
-        adj = np.ascontiguousarray(np.asarray(adjacency, dtype=np.int32))
-        if adj.ndim != 2:
-            raise ValueError("adjacency must be rectangular (n_centres, k); ragged radius mode is not supported")
+        and permutation like the reference (mmd_searchlight_null_pc).  `adjacency` may be ragged (radius mode)."""
+        ragged = self._is_ragged(adjacency)
+        if ragged:
+            rows = [np.asarray(r, dtype=np.int32).ravel() for r in adjacency]
+            n = len(rows)
+            offsets = np.zeros(n + 1, dtype=np.int64)
+            np.cumsum([len(r) for r in rows], out=offsets[1:])
+            indices = np.ascontiguousarray(np.concatenate(rows)) if n else np.zeros(0, dtype=np.int32)
+            anc = None if anchors is None else np.ascontiguousarray(np.asarray(anchors, dtype=np.int32))
+        else:
+            adj = np.ascontiguousarray(np.asarray(adjacency, dtype=np.int32))
+            if adj.ndim != 2:
+                raise ValueError("adjacency must be (n_centres, k) or a sequence of index arrays")
+            n, k = adj.shape
         pt = np.ascontiguousarray(np.asarray(perm_test, dtype=np.int32))
         pi = np.ascontiguousarray(np.asarray(perm_imagery, dtype=np.int32))
-        n, k = adj.shape
         per_centre = pi.ndim == 3
         if pt.ndim != 2 or pi.ndim not in (2, 3) or pi.shape[-2] != len(pt) or (per_centre and len(pi) != n):
             raise ValueError("perm_test (n_perm, n_test) and perm_imagery (n_perm, n_imagery) or (n_centres, n_perm, n_imagery) "
@@ -263,9 +272,15 @@ class Engine:
         flags = np.zeros(n, dtype=np.int32)
         null = np.empty((n, n_perm, _lib.N_NULL_SCORES), dtype=np.float64)
         shared = np.ascontiguousarray(pi[0]) if per_centre else pi
-        self._check(self._lib.mmd_searchlight_null_pc(self._h, adj.ctypes.data, n, k, float(alpha), pt.ctypes.data,
-                                                      shared.ctypes.data, pi.ctypes.data if per_centre else None, n_perm,
-                                                      scores.ctypes.data, flags.ctypes.data, null.ctypes.data))
+        pc = pi.ctypes.data if per_centre else None
+        if ragged:
+            self._check(self._lib.mmd_searchlight_null_ragged(
+                self._h, indices.ctypes.data, offsets.ctypes.data, None if anc is None else anc.ctypes.data, n, float(alpha),
+                pt.ctypes.data, shared.ctypes.data, pc, n_perm, scores.ctypes.data, flags.ctypes.data, null.ctypes.data))
+        else:
+            self._check(self._lib.mmd_searchlight_null_pc(self._h, adj.ctypes.data, n, k, float(alpha), pt.ctypes.data,
+                                                          shared.ctypes.data, pc, n_perm, scores.ctypes.data,
+                                                          flags.ctypes.data, null.ctypes.data))
         return scores, flags, null
 
     # -- eval.py primitives (arbitrary shapes, float64) -----------------------------------------

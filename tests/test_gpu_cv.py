@@ -72,3 +72,43 @@ def test_cv_errors(engine, golden_dir):
         engine.searchlight_cv(A, [1.0], [0, 100, 200])
     with pytest.raises(RuntimeError, match="alpha must be positive"):
         engine.searchlight_cv(A, [0.0], [0, 150, len(tr)])
+
+
+def test_searchlight_cli_with_an_alpha_grid(tmp_path, monkeypatch):
+    """`--l2-regularization-alphas`: a cross-validated ridge per vertex; the pickle carries the selected alpha per vertex and
+    the scores are those of the oracle's fit with that alpha."""
+    import pickle
+    from multimodal_decoding_b200 import data as d
+    import multimodal_decoding_b200.analyses.decoding.searchlight.searchlight as sl
+    monkeypatch.setattr(sl, "SEARCHLIGHT_OUT_DIR", str(tmp_path))
+    d.set_data_provider(d.SyntheticProvider(n_train=300, nan_fraction=0.08, seed=3))
+    try:
+        args = sl.get_args(["--model", "clip", "--n-neighbors", "40", "--training-mode", "agnostic", "--subjects", "sub-01",
+                            "--hemis", "left", "--resolution", "fsaverage3", "--l2-regularization-alphas", "1", "1000", "100000"])
+        sl.run(args)
+        cfg = d.LatentFeatsConfig("clip", logging=False)
+        path = sl.get_results_file_path(cfg, "left", "sub-01", "agnostic", "fsaverage3", "n_neighbors_40", "cv")
+        res = pickle.load(open(path, "rb"))
+        V = int((~res["nan_locations"]).sum())
+        assert res["best_alpha"].shape == (V,) and res["mean_test_score"].shape == (V, 3)
+        assert set(np.unique(res["best_alpha"])) <= {1.0, 1000.0, 100000.0}
+        tr_f, _, _ = d.get_fmri_surface_data("", "sub-01", d.SPLIT_TRAIN, "agnostic", "left", "fsaverage3")
+        te_f, _, _ = d.get_fmri_surface_data("", "sub-01", d.SPLIT_TEST, hemi="left", resolution="fsaverage3")
+        im_f, _, _ = d.get_fmri_surface_data("", "sub-01", d.SPLIT_IMAGERY, hemi="left", resolution="fsaverage3")
+        tr_f, te_f, im_f = d.standardize_fmri_betas(tr_f, te_f, im_f)
+        lat = [d.get_latent_features(cfg, "sub-01", s) for s in (d.SPLIT_TRAIN, d.SPLIT_TEST, d.SPLIT_IMAGERY)]
+        lat = np.concatenate(d.standardize_latents(*lat)).astype(np.float16)
+        X = np.concatenate((tr_f, te_f, im_f)).astype(np.float16)
+        ntr, nte = len(tr_f), len(te_f)
+        ids = (np.arange(ntr), np.arange(ntr, ntr + nte), np.arange(ntr + nte, ntr + nte + len(im_f)))
+        for c in range(0, V, 61):
+            nb = res["adjacency"][c]
+            fs = orc.grid_search_fold_scores(X[:ntr][:, nb].astype(np.float64), lat[:ntr].astype(np.float64), [1.0, 1000.0, 100000.0], 5)
+            mean = np.average(fs, axis=1)
+            assert np.array_equal(mean, res["mean_test_score"][c])
+            alpha = [1.0, 1000.0, 100000.0][int(np.argmax(mean))]
+            assert alpha == res["best_alpha"][c]
+            want = orc.search_light(X, lat, res["adjacency"], *ids, alpha, orc.default_is_caption(nte), [c])
+            assert np.array_equal(np.array([res["scores"][c][k] for k in orc.SCORE_KEYS]), want[0])
+    finally:
+        d.set_data_provider(d.SyntheticProvider())

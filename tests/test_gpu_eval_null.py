@@ -81,6 +81,13 @@ def test_null_distribution_matches_reference(golden_dir, tmp_path):
     per_centre = np.stack([g["derangements"][g["derangement_choice"][ci]] for ci in range(len(g["centres"]))])
     scores, flags, null = eng.searchlight_null(g["adjacency"][g["centres"]], 1.0, g["perms"], per_centre)
     assert flags.sum() == 0 and np.array_equal(null, g["null_scores"])
+    # ragged (radius-mode) neighbourhoods go through the same branch (mmd_searchlight_null_ragged)
+    rows = [g["adjacency"][c] for c in g["centres"]]
+    ragged = [rows[0], rows[1][:-5], rows[2]]
+    s_r, f_r, null_r = eng.searchlight_null(ragged, 1.0, g["perms"], per_centre)
+    assert f_r.sum() == 0 and np.array_equal(null_r[[0, 2]], g["null_scores"][[0, 2]])
+    s_1, _, null_1 = eng.searchlight_null(rows[1][None, :-5], 1.0, g["perms"], per_centre[[1]])
+    assert np.array_equal(null_r[1], null_1[0]) and np.array_equal(s_r[1], s_1[0])
     a = nd.draw_imagery_permutations(5, 3, n_centres=4, seed=7)
     assert a.shape == (4, 5, 3) and np.array_equal(a, nd.draw_imagery_permutations(5, 3, n_centres=4, seed=7))
     assert {tuple(r) for r in a.reshape(-1, 3)} <= {(1, 2, 0), (2, 0, 1)} and nd.draw_imagery_permutations(5, 3).shape == (5, 3)
