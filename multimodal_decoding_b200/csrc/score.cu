@@ -25,11 +25,17 @@ namespace mmd {
 namespace {
 constexpr int THREADS = 576;              // 18 warps: 2 row halves x 9 column groups; one CTA per SM
 constexpr int MT = 5;                     // m-tiles per warp and pass (40 rows)
-constexpr int KC = 16, LDS = KC + 4;
+#ifndef MMD_SCORE_KC
+#define MMD_SCORE_KC 16
+#endif
+#ifndef MMD_SCORE_STAGES
+#define MMD_SCORE_STAGES 4
+#endif
+constexpr int KC = MMD_SCORE_KC, LDS = KC + 4;
 constexpr int PASS_ROWS = 80;             // 10 m-tiles per pass, two passes cover 152 rows (19 tiles + 1 idle)
 constexpr int RAW_ROW0 = EVAL_PAD;        // first un-standardised imagery row
 constexpr int M_ROWS = YHAT_ROWS;
-constexpr int STAGES = 4;
+constexpr int STAGES = MMD_SCORE_STAGES;
 constexpr int A_STAGE = PASS_ROWS * LDS, B_STAGE = EVAL_PAD * LDS;   // doubles per stage
 constexpr int CHUNKS = (PASS_ROWS + EVAL_PAD) * (KC / 2);             // 16-byte copies per stage
 static_assert(M_ROWS <= 2 * PASS_ROWS && 2 * PASS_ROWS <= 5 * 32, "row-norm threads: two per row, warps 0-4");
