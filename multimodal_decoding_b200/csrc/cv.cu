@@ -19,9 +19,9 @@ namespace mmd {
 namespace {
 constexpr int THREADS = 576;              // 18 warps: 2 row halves x 9 column groups (the layout of score.cu)
 constexpr int MT = 5;
-constexpr int KC = 16, LDS = KC + 4;
+constexpr int KC = 32, LDS = KC + 4;           // 32-feature chunks, three stages (as score.cu)
 constexpr int PASS_ROWS = 80;
-constexpr int STAGES = 4;
+constexpr int STAGES = 3;
 constexpr int A_STAGE = PASS_ROWS * LDS, B_STAGE = EVAL_PAD * LDS;
 constexpr int CHUNKS = (PASS_ROWS + EVAL_PAD) * (KC / 2);
 }  // namespace

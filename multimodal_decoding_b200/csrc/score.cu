@@ -7,7 +7,7 @@
 // Row layout of yhat / candidates (set up by the host and predict.cu): [captions | images | imagery | zero pad],
 // rows 144..146 of yhat are the un-standardised imagery predictions (the *_no_std scores).
 // One CTA per centre.  The (152 x 144) x Dp inner products run on the fp64 tensor pipe in two passes of 80
-// rows; both operands are float64 in global memory and go through a 4-stage cp.async ring, so the loop has
+// rows; both operands are float64 in global memory and go through a 3-stage cp.async ring of 32-feature chunks (A/B of 16 x 4 vs 32 x 3: score stage -3 %), so the loop has
 // the same shape as predict.cu's.  Row norms are accumulated from the staged tiles.
 //
 // Guard for the integer prediction GEMM (predict_i8.cu): that kernel's predictions carry a bounded truncation error
@@ -26,10 +26,10 @@ namespace {
 constexpr int THREADS = 576;              // 18 warps: 2 row halves x 9 column groups; one CTA per SM
 constexpr int MT = 5;                     // m-tiles per warp and pass (40 rows)
 #ifndef MMD_SCORE_KC
-#define MMD_SCORE_KC 16
+#define MMD_SCORE_KC 32
 #endif
 #ifndef MMD_SCORE_STAGES
-#define MMD_SCORE_STAGES 4
+#define MMD_SCORE_STAGES 3
 #endif
 constexpr int KC = MMD_SCORE_KC, LDS = KC + 4;
 constexpr int PASS_ROWS = 80;             // 10 m-tiles per pass, two passes cover 152 rows (19 tiles + 1 idle)

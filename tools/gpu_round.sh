@@ -12,7 +12,7 @@ KREG='regex:(factor_solve|predict_kernel|predict_i8|slice_|col(max|scale)_kernel
 timeout 600 python bench.py $SMALL > gpurun_out/bench_small.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" -c 400 --csv \
    --log-file gpurun_out/launches.csv python bench.py $SMALL > gpurun_out/ncu_launches.log 2>&1
-for kn in predict_kernel score_kernel; do
+for kn in predict_i8_kernel score_kernel; do
   timeout 900 ncu --set full --clock-control none --import-source on -k $kn -s 0 -c 1 -f -o gpurun_out/${kn} \
      python bench.py $SMALL > gpurun_out/ncu_${kn}.log 2>&1
 done
