@@ -253,6 +253,10 @@ int mmd_set_group_size(mmd_handle* h, int group_size);
  *   0            float64 tensor pipe (DMMA) for every centre.
  * The environment variable MMD_B200_PREDICT=f64 selects 0 at mmd_create. */
 int mmd_set_predict_mode(mmd_handle* h, int mode);
+/* Cluster-union Gram: 1 (default) = exact integer arithmetic on tcgen05 (six 7-bit digits per float16 beta, int32 accumulators
+ * in tensor memory; a cluster whose betas are not exact in six digits is redone by the float64 kernel), 0 = float64 DMMA kernel.
+ * Environment override at mmd_create: MMD_B200_SYRK=f64. */
+int mmd_set_syrk_mode(mmd_handle* h, int mode);
 
 /* Diagnostics: after the next mmd_searchlight* call mmd_get_margins returns, per centre, the smallest absolute
  * difference between a prediction's distance to its own candidate and to any other candidate it is compared with

@@ -17,7 +17,7 @@ EXPORTS = [
     "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
     "mmd_searchlight_null", "mmd_searchlight_null_pc", "mmd_searchlight_null_ragged", "mmd_searchlight_cv", "mmd_ridge_load", "mmd_ridge_cv", "mmd_ridge_fit", "mmd_ridge_predict", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
     "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels", "mmd_check_guards", "mmd_guard_selftest",
-    "mmd_set_predict_mode", "mmd_enable_margins", "mmd_get_margins",
+    "mmd_set_predict_mode", "mmd_set_syrk_mode", "mmd_enable_margins", "mmd_get_margins",
 ]
 
 _lib = None
@@ -103,6 +103,8 @@ def load():
     lib.mmd_get_counters.restype = i32
     lib.mmd_set_predict_mode.argtypes = [vp, i32]
     lib.mmd_set_predict_mode.restype = i32
+    lib.mmd_set_syrk_mode.argtypes = [vp, i32]
+    lib.mmd_set_syrk_mode.restype = i32
     lib.mmd_enable_margins.argtypes = [vp, i32]
     lib.mmd_enable_margins.restype = i32
     lib.mmd_get_margins.argtypes = [vp, vp, i32]

@@ -198,6 +198,9 @@ struct mmd_handle {
     struct PlanCache* plan_cache = nullptr;     // clusters / unions / groups of the last adjacency (run_searchlight)
     int64_t plan_hits = 0;
     int predict_mode = 1;           // 1: tcgen05 int8 digit GEMM + float64 reroute of guarded centres; 0: float64 DMMA kernel
+    int syrk_mode = 1;              // 1: exact integer cluster Gram on tcgen05 (syrk_i8.cu); 0: float64 DMMA kernel
+    DevBuf syrk_planes, syrk_scales, syrk_flags, syrk_status;
+    size_t syrk_plane_rows = 0;     // rows of the current chunk's plane tensor (largest batch)
     int n_sms = 148;
     int call_batches = 0;           // batches of the current searchlight call (index into reroute_counts)
     bool want_margins = false;
@@ -580,6 +583,7 @@ int run_batch_cv(mmd_handle* h, const SolveParams& base, const std::vector<GemmP
     for (int f = 0; f < cv.n_folds; ++f)
         for (int c = 0; c < n_cl; ++c) {
             GemmProblem p = probs[c];
+            p.only_if = nullptr;                             // fold Grams always run on the float64 kernel
             p.A = p.B = cv.xfold[f].as<__half>();
             p.lda = p.ldb = cv.ld[f];
             p.K = cv.ld[f];
@@ -748,6 +752,35 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
                  o_unoff = place((size_t)n_all * sizeof(long)), o_unn = place((size_t)n_all * sizeof(int)),
                  o_coff = place((size_t)n_all * sizeof(long)), o_cn = place((size_t)n_all * sizeof(int)),
                  o_tasks = place((size_t)n_all * sizeof(CentreTask)), o_probs = place((size_t)n_cl * sizeof(GemmProblem));
+    // exact integer SYRK (syrk_i8.cu): per cluster six digit planes of `up` rows, 128 x 128 lower-triangle tiles
+    const bool syrk_i8 = h->syrk_mode == 1 && h->ldt % 64 == 0;
+    std::vector<SyrkCluster> sy_cl;
+    std::vector<SyrkItem> sy_items;
+    long plane_rows = 0;
+    if (syrk_i8) {
+        long scale_off = 0;
+        sy_cl.resize(n_cl);
+        for (int c = 0; c < n_cl; ++c) {
+            const int u = probs[c].M, up = round_up(u, 128);
+            SyrkCluster& sc = sy_cl[c];
+            sc.row_base = plane_rows;
+            sc.u = u;
+            sc.up = up;
+            sc.rows = probs[c].rowsA;
+            sc.scales = h->syrk_scales.as<double>() + scale_off;
+            sc.inexact = h->syrk_flags.as<int>() + c;
+            sc.C = probs[c].C;
+            sc.ldc = probs[c].ldc;
+            probs[c].only_if = sc.inexact;                 // the float64 kernel redoes a cluster that was not exact
+            for (int m0 = 0; m0 < up; m0 += 128)
+                for (int n0 = 0; n0 <= m0; n0 += 128)
+                    sy_items.push_back(SyrkItem{(int)(plane_rows + m0), (int)(plane_rows + n0), up, c, m0, n0});
+            plane_rows += 6L * up;
+            scale_off += up;
+        }
+        if ((size_t)plane_rows > h->syrk_plane_rows) return fail(h, "internal: digit-plane buffer too small");
+    }
+    const size_t o_sycl = place(sy_cl.size() * sizeof(SyrkCluster)), o_syit = place(sy_items.size() * sizeof(SyrkItem));
     const int half = h->batch_half;
     h->batch_half ^= 1;
     if (!h->batch_copied[half]) CU(cudaEventCreateWithFlags(&h->batch_copied[half], cudaEventDisableTiming));
@@ -764,6 +797,8 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
         memcpy(hp + o_cn, task_core_n.data(), (size_t)n_all * sizeof(int));
         memcpy(hp + o_tasks, tasks.data(), (size_t)n_all * sizeof(CentreTask));
         memcpy(hp + o_probs, probs.data(), (size_t)n_cl * sizeof(GemmProblem));
+        if (!sy_cl.empty()) memcpy(hp + o_sycl, sy_cl.data(), sy_cl.size() * sizeof(SyrkCluster));
+        if (!sy_items.empty()) memcpy(hp + o_syit, sy_items.data(), sy_items.size() * sizeof(SyrkItem));
     }
     CU(cudaMemcpyAsync(h->batch_dev.p, h->batch_host[half].p, blk, cudaMemcpyHostToDevice, h->stream));
     CU(cudaEventRecord(h->batch_copied[half], h->stream));
@@ -780,8 +815,15 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     span_end(h);
 
     span_begin(h, ST_SYRK);
-    CU(launch_gemm_gather(probs_dev, n_cl, max_u, max_u, h->stream));
-    span_end(h);
+    if (syrk_i8) {
+        const SyrkCluster* sycl_dev = reinterpret_cast<const SyrkCluster*>(dp + o_sycl);
+        CU(cudaMemsetAsync(h->syrk_flags.p, 0, (size_t)n_cl * sizeof(int), h->stream));
+        CU(launch_slice_union(h->Xt.as<__half>(), h->ldt, sycl_dev, n_cl, max_u, h->syrk_planes.as<int8_t>(), h->stream));
+        CU(launch_syrk_i8(h->syrk_planes.as<int8_t>(), plane_rows, h->ldt, reinterpret_cast<const SyrkItem*>(dp + o_syit),
+                          (int)sy_items.size(), sycl_dev, h->n_sms, h->syrk_status.as<int>(), h->stream));
+    }
+    CU(launch_gemm_gather(probs_dev, n_cl, max_u, max_u, h->stream));      // with syrk_i8: only the clusters flagged inexact
+    span_end(h, syrk_i8 ? 3 : 1);
 
     SolveParams sp{};
     sp.tasks = tasks_dev;
@@ -970,6 +1012,28 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
     CU(h->core_work.ensure(std::max<size_t>((size_t)max_core * (sp_max + EVAL_PAD) * sp_max, 1) * sizeof(double)));
     CU(h->group_flags.ensure(std::max<size_t>(max_core, 1) * sizeof(int)));
     if (with_null) CU(h->dist.ensure((size_t)max_tasks * NULL_DIST_ROWS * EVAL_PAD * sizeof(double)));
+    if (h->syrk_mode == 1 && h->ldt % 64 == 0) {
+        size_t max_rows = 0, max_scales = 0, max_cl = 0;
+        for (size_t b = 0; b + 1 < batch_start.size(); ++b) {
+            size_t rows_b = 0, sc_b = 0;
+            for (int c = batch_start[b]; c < batch_start[b + 1]; ++c) {
+                const size_t up = (size_t)round_up((int)(plan.un_off[c + 1] - plan.un_off[c]), 128);
+                rows_b += 6 * up;
+                sc_b += up;
+            }
+            max_rows = std::max(max_rows, rows_b);
+            max_scales = std::max(max_scales, sc_b);
+            max_cl = std::max<size_t>(max_cl, batch_start[b + 1] - batch_start[b]);
+        }
+        CU(h->syrk_planes.ensure(max_rows * h->ldt));
+        h->syrk_plane_rows = h->syrk_planes.bytes / h->ldt;
+        CU(h->syrk_scales.ensure(std::max<size_t>(max_scales, 1) * sizeof(double)));
+        CU(h->syrk_flags.ensure(std::max<size_t>(max_cl, 1) * sizeof(int)));
+        if (!h->syrk_status.p) {
+            CU(h->syrk_status.ensure(sizeof(int)));
+            CU(cudaMemsetAsync(h->syrk_status.p, 0, sizeof(int), h->stream));
+        }
+    }
     if (h->cv) {
         h->cv->pool_stride = std::max(h->cv->pool_stride, max_pool);
         CU(h->cv->pool.ensure((size_t)h->cv->n_folds * h->cv->pool_stride * sizeof(double)));
@@ -1202,7 +1266,8 @@ std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
                       &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->perm_im_centre, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval,
                       &h->xplanes, &h->sX, &h->colmax, &h->zplanes, &h->sZ, &h->amp2, &h->i8_status, &h->reroute_list,
-                      &h->reroute_counts, &h->margins, &h->active, &h->batch_dev};
+                      &h->reroute_counts, &h->margins, &h->active, &h->batch_dev, &h->syrk_planes, &h->syrk_scales, &h->syrk_flags,
+                      &h->syrk_status};
 }
 
 // the stream must have passed mmd_upload's kernels (any later synchronisation of h->stream will do)
@@ -1215,6 +1280,14 @@ void release_upload_staging(mmd_handle* h) {
 
 // after the stream is synchronised: how many centres went back to the float64 kernels; protocol errors of the integer GEMM
 int collect_i8_stats(mmd_handle* h) {
+    if (h->syrk_status.p) {
+        int st = 0;
+        CU(cudaMemcpy(&st, h->syrk_status.p, sizeof(int), cudaMemcpyDeviceToHost));
+        if (st) {
+            cudaMemset(h->syrk_status.p, 0, sizeof(int));
+            return fail(h, "syrk_i8_kernel: a bounded wait ran out (role %d); results are not valid", st);
+        }
+    }
     if (h->call_batches == 0) return 0;
     std::vector<int> counts(h->call_batches);
     int status = 0;
@@ -1274,6 +1347,7 @@ int mmd_create(int device, mmd_handle** out) {
     }
     cudaDeviceGetAttribute(&h->n_sms, cudaDevAttrMultiProcessorCount, device);
     if (const char* e = getenv("MMD_B200_PREDICT")) h->predict_mode = strcmp(e, "f64") == 0 ? 0 : 1;
+    if (const char* e = getenv("MMD_B200_SYRK")) h->syrk_mode = strcmp(e, "f64") == 0 ? 0 : 1;
     *out = h;
     return 0;
 }
@@ -1381,6 +1455,14 @@ int mmd_set_predict_mode(mmd_handle* h, int mode) {
     if (mode == 1 && h->uploaded && !h->xplanes.p)
         return fail(h, "mmd_set_predict_mode: switch to the integer GEMM before mmd_upload (its digit planes are cut there)");
     h->predict_mode = mode;
+    return 0;
+}
+
+int mmd_set_syrk_mode(mmd_handle* h, int mode) {
+    if (!h) return 1;
+    if (mode != 0 && mode != 1) return fail(h, "mmd_set_syrk_mode: mode must be 0 (float64 DMMA) or 1 (exact integer SYRK on tcgen05)");
+    h->syrk_mode = mode;
+    if (h->plan_cache) h->plan_cache->valid = false;
     return 0;
 }
 

@@ -25,6 +25,7 @@ __global__ void __launch_bounds__(256, 2) gemm_nt_f16_f64_kernel(const GemmProbl
     __half* Bs = As + STAGES * A_STAGE;
 
     const GemmProblem p = probs[blockIdx.z];
+    if (p.only_if && *p.only_if == 0) return;
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
     if (m0 >= p.M || n0 >= p.N) return;
     if (p.lower_only && n0 > m0 + BM - 1) return;

@@ -28,9 +28,33 @@ struct GemmProblem {
     long ldc;           // even
     int lower_only;     // skip tiles strictly above the diagonal (symmetric rank-k update)
     int scatter_c;      // 1: row i of the product is written to C row rowsA[i] (a row subset of a full-size result)
+    const int* only_if; // optional (device): the problem is skipped unless *only_if != 0 (float64 redo of a cluster whose
+                        // betas were not exact in the integer SYRK's six digits, syrk_i8.cu)
 };
 size_t gemm_gather_smem_bytes();
 cudaError_t launch_gemm_gather(const GemmProblem* probs_dev, int n_problems, int max_m, int max_n, cudaStream_t s);
+
+// ---- syrk_i8.cu ---------------------------------------------------------------------------
+// exact integer cluster Gram on tcgen05 (see the file header); planes: per cluster six digit planes of `up` rows x ldt bytes
+struct SyrkCluster {
+    long row_base;        // first row of the cluster's plane 0 in the batch's plane tensor
+    int u, up;            // union size, rounded up to 128 (row stride between the planes)
+    const int* rows;      // the union's vertex ids (device)
+    double* scales;       // (up) power-of-two scale of every union row, written by the slicing kernel
+    int* inexact;         // set when a row is not exact in six digits: the float64 kernel redoes this cluster
+    double* C;            // the cluster's Gram (u x ldc, lower triangle written)
+    long ldc;
+};
+struct SyrkItem {
+    int row_a, row_b;     // plane-0 tensor rows of the tile's rows (m0) and columns (n0)
+    int up, cluster;
+    int m0, n0;           // n0 <= m0: lower-triangle tiles
+};
+size_t syrk_i8_smem_bytes();
+cudaError_t launch_slice_union(const __half* Xt, int ldt, const SyrkCluster* clusters_dev, int n_clusters, int max_u, int8_t* planes,
+                               cudaStream_t s);
+cudaError_t launch_syrk_i8(const int8_t* planes, long plane_rows, int ldt, const SyrkItem* items_dev, int n_items,
+                           const SyrkCluster* clusters_dev, int n_sms, int* status, cudaStream_t s);
 
 // ---- factor_solve.cu ---------------------------------------------------------------------
 // One searchlight centre = one CTA.  All pointers are device pointers.

@@ -375,6 +375,10 @@ class Engine:
         Call before upload()."""
         self._check(self._lib.mmd_set_predict_mode(self._h, int(mode)))
 
+    def set_syrk_mode(self, mode: int):
+        """1 = exact integer cluster Gram on tcgen05 (default), 0 = float64 DMMA kernel."""
+        self._check(self._lib.mmd_set_syrk_mode(self._h, int(mode)))
+
     def enable_margins(self, on=True):
         self._check(self._lib.mmd_enable_margins(self._h, 1 if on else 0))
 

@@ -329,6 +329,25 @@ def test_neighbourhood_and_feature_sweep(engine, k, n_dims):
     assert np.array_equal(got[sample], want)
 
 
+def test_integer_syrk_matches_float64_syrk(engine, golden_dir):
+    """The cluster Gram on tcgen05 (exact six-digit integer arithmetic, syrk_i8.cu) against the float64 DMMA kernel: identical
+    scores (both equal the reference's fixture) and predictions that agree to rounding level."""
+    g = np.load(os.path.join(golden_dir, "searchlight_smooth.npz"))
+    tr, te, im = _ids(g)
+    engine.upload(g["X"], g["latents"], tr, te, im, orc.default_is_caption(len(te)))
+    nb = g["adjacency"][17]
+    out = {}
+    try:
+        for mode in (0, 1):
+            engine.set_syrk_mode(mode)
+            scores, flags = engine.searchlight(g["adjacency"], float(g["alpha"]))
+            assert flags.sum() == 0 and np.array_equal(scores, g["scores"]), mode
+            out[mode] = engine.predict_centre(nb, float(g["alpha"]))
+    finally:
+        engine.set_syrk_mode(1)
+    assert np.abs(out[0] - out[1]).max() <= 1e-11 * np.abs(out[0]).max()
+
+
 def test_knn_k1500_on_the_level7_mesh(engine):
     """k = 1500 (BASELINE.json configs[3]) on the full-size mesh (163,842 vertices): the radix-select keeps at most 2048
     candidates per query, so the call must not report an overflow on a near-regular mesh, and the rows equal brute force."""

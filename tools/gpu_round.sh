@@ -8,7 +8,7 @@ timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo 
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2>&1
 timeout 900 python bench.py > gpurun_out/bench.log 2>&1; echo "bench rc=$?" >> gpurun_out/bench.log
 SMALL="--centres-per-step 12288 --steps 2 --warmup 1 --no-e2e --no-cpu-baseline"
-KREG='regex:(factor_solve|predict_kernel|predict_i8|slice_|col(max|scale)_kernel|score_kernel|gemm_nt|prep_tasks|pack_transpose|knn_kernel|radius_kernel|half_to_double|row_sqnorm|gather_rows)'
+KREG='regex:(factor_solve|predict_kernel|predict_i8|slice_|syrk_i8|col(max|scale)_kernel|score_kernel|gemm_nt|prep_tasks|pack_transpose|knn_kernel|radius_kernel|half_to_double|row_sqnorm|gather_rows)'
 timeout 600 python bench.py $SMALL > gpurun_out/bench_small.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" -c 400 --csv \
    --log-file gpurun_out/launches.csv python bench.py $SMALL > gpurun_out/ncu_launches.log 2>&1
