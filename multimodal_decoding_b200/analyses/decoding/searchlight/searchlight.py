@@ -144,23 +144,51 @@ def _is_caption_mask(n_test):
     return st == "caption"
 
 
+_PYHELPERS = None
+
+
+def _pyhelpers():
+    """libmmd_pyhelpers.so (csrc/pydicts.c) through ctypes.PyDLL, or False when it was not built / does not match this Python."""
+    global _PYHELPERS
+    if _PYHELPERS is None:
+        import ctypes
+        import sys
+        path = os.path.join(os.path.dirname(os.path.abspath(sys.modules["multimodal_decoding_b200"].__file__)),
+                            "libmmd_pyhelpers.so")
+        try:
+            lib = ctypes.PyDLL(path)
+            lib.mmd_build_score_dicts.restype = ctypes.py_object
+            lib.mmd_build_score_dicts.argtypes = [ctypes.py_object, ctypes.c_void_p, ctypes.c_ssize_t, ctypes.c_void_p]
+            probe = np.empty(2, dtype=object)
+            lib.mmd_build_score_dicts(("a", "b"), np.array([[1.0, 2.0], [3.0, 4.0]]).ctypes.data, 2, probe.ctypes.data)
+            _PYHELPERS = lib if probe[1] == {"a": 3.0, "b": 4.0} else False
+        except (OSError, AttributeError):
+            _PYHELPERS = False
+    return _PYHELPERS
+
+
 def _scores_to_dicts(scores: np.ndarray) -> np.ndarray:
-    """(n, 8) float64 block -> the reference's object array of 8-key dicts (searchlight.py:114, :149).  The cyclic
-    garbage collector is paused while the n dicts are created (they hold only floats); a dict display over the
-    unpacked columns is the fastest way CPython offers to build them (60 ms for a 163,842-vertex hemisphere)."""
+    """(n, 8) float64 block -> the reference's object array of 8-key dicts (searchlight.py:114, :149).  The dicts are built
+    through the CPython API by csrc/pydicts.c when that helper is present (about 40 ms for a 163,842-vertex hemisphere),
+    else by a dict display over the unpacked columns, the fastest way pure Python offers (about 80 ms); the cyclic garbage
+    collector is paused meanwhile (the dicts hold only floats)."""
     import gc
     keys = score_keys()
-    scores = np.asarray(scores, dtype=np.float64)
+    scores = np.ascontiguousarray(np.asarray(scores, dtype=np.float64))
     out = np.empty(len(scores), dtype=object)
-    cols = [c.tolist() for c in scores.T]
     was_enabled = gc.isenabled()
     gc.disable()
     try:
-        if len(keys) == 8:
+        lib = _pyhelpers()
+        if lib and scores.ndim == 2 and scores.shape[1] == len(keys) and len(scores):
+            lib.mmd_build_score_dicts(tuple(keys), scores.ctypes.data, len(scores), out.ctypes.data)
+        elif len(keys) == 8:
+            cols = [c.tolist() for c in scores.T]
             k0, k1, k2, k3, k4, k5, k6, k7 = keys
             out[:] = [{k0: a0, k1: a1, k2: a2, k3: a3, k4: a4, k5: a5, k6: a6, k7: a7}
                       for a0, a1, a2, a3, a4, a5, a6, a7 in zip(*cols)]
         else:
+            cols = [c.tolist() for c in scores.T]
             out[:] = [dict(zip(keys, row)) for row in zip(*cols)]
     finally:
         if was_enabled:

@@ -43,7 +43,27 @@ def build(force=False, verbose=False, variant=None, defines=()):
     if failed:
         raise RuntimeError("nvcc failed")
     subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib] + objs + ["-lcudart"])
+    if not variant:
+        build_pyhelpers()
     return lib
+
+
+PYHELPERS = os.path.join(HERE, "libmmd_pyhelpers.so")
+
+
+def build_pyhelpers():
+    """The CPython-API helper of the mirror (csrc/pydicts.c, plain C, no CUDA).  Optional: without Python.h the mirror
+    builds its score dicts in Python."""
+    import sysconfig
+    inc = sysconfig.get_paths()["include"]
+    if not os.path.exists(os.path.join(inc, "Python.h")):
+        return None
+    try:
+        subprocess.check_call([os.environ.get("CC", "gcc"), "-O2", "-shared", "-fPIC", f"-I{inc}",
+                               os.path.join(CSRC, "pydicts.c"), "-o", PYHELPERS])
+    except (OSError, subprocess.CalledProcessError):
+        return None
+    return PYHELPERS
 
 
 if __name__ == "__main__":
