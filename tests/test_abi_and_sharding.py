@@ -64,6 +64,31 @@ def test_estimator_protocol_and_score_dicts():
     assert isinstance(sl._rectangular([np.arange(3), np.arange(5)]), list)
 
 
+def test_score_dicts_helper_matches_python_construction():
+    """csrc/pydicts.c (CPython API) and the pure-Python construction give the same object array of dicts."""
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+    from multimodal_decoding_b200.engine import score_keys
+    rng = np.random.default_rng(3)
+    block = rng.random((1000, 8))
+    block[7, 3] = np.nan
+    got = sl._scores_to_dicts(block)
+    keys = score_keys()
+    assert got.dtype == object and got.shape == (1000,)
+    for i in (0, 7, 999):
+        assert type(got[i]) is dict and list(got[i].keys()) == list(keys)
+        want = dict(zip(keys, block[i].tolist()))
+        assert all((got[i][k] == want[k]) or (np.isnan(got[i][k]) and np.isnan(want[k])) for k in keys)
+        assert all(type(v) is float for v in got[i].values())
+    if sl._pyhelpers():                                        # built wherever Python.h is present
+        saved = sl._PYHELPERS
+        try:
+            sl._PYHELPERS = False
+            slow = sl._scores_to_dicts(block)
+        finally:
+            sl._PYHELPERS = saved
+        assert all(list(a.items())[:3] == list(b.items())[:3] for a, b in zip(got[:7], slow[:7]))
+
+
 def test_split_bounds_equals_array_split():
     from multimodal_decoding_b200.sharding import split_bounds, spatial_order
     for n, parts in ((163842, 8), (10, 3), (7, 7), (5, 8)):
