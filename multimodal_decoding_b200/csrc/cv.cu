@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(THREADS, 1) cv_score_kernel(CvScoreParams prm)
             for (int i = 0; i < MT; ++i)
 #pragma unroll
                 for (int j = 0; j < 2; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-            double sq = 0.0;
+            double sq = 0.0, sq2 = 0.0;
 
             for (int s = 0; s < STAGES - 1; ++s) {
                 if (s < nk) load_stage(s, s);
@@ -93,13 +93,13 @@ __global__ void __launch_bounds__(THREADS, 1) cv_score_kernel(CvScoreParams prm)
                     cp_async_commit();
                 }
                 const double* a_st = As + (kc % STAGES) * A_STAGE;
-                if (ti == 0 && tid < 2 * PASS_ROWS) {
-                    const double* x = a_st + (tid >> 1) * LDS + (tid & 1) * (KC / 2);
+                if (ti == 0 && tid < 4 * PASS_ROWS) {      // four threads per row, two independent chains each
+                    const double* x = a_st + (tid >> 2) * LDS + (tid & 3) * (KC / 4);
 #pragma unroll
-                    for (int e = 0; e < KC / 2; e += 2) {
+                    for (int e = 0; e < KC / 4; e += 2) {
                         const double2 v = *reinterpret_cast<const double2*>(x + e);
                         sq = fma(v.x, v.x, sq);
-                        sq = fma(v.y, v.y, sq);
+                        sq2 = fma(v.y, v.y, sq2);
                     }
                 }
                 const double* as = a_st + (wm * MT * 8 + fr) * LDS + fk;
@@ -116,9 +116,11 @@ __global__ void __launch_bounds__(THREADS, 1) cv_score_kernel(CvScoreParams prm)
                 }
             }
             cp_async_wait<0>();
-            if (ti == 0 && tid < 2 * PASS_ROWS) {
+            if (ti == 0 && tid < 4 * PASS_ROWS) {
+                sq += sq2;
                 sq += __shfl_xor_sync(0xffffffffu, sq, 1);
-                if ((tid & 1) == 0) nrm_sm[row0 + (tid >> 1)] = sq;
+                sq += __shfl_xor_sync(0xffffffffu, sq, 2);
+                if ((tid & 3) == 0) nrm_sm[row0 + (tid >> 2)] = sq;
             }
             __syncthreads();
 

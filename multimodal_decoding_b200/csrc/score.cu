@@ -38,7 +38,7 @@ constexpr int M_ROWS = YHAT_ROWS;
 constexpr int STAGES = MMD_SCORE_STAGES;
 constexpr int A_STAGE = PASS_ROWS * LDS, B_STAGE = EVAL_PAD * LDS;   // doubles per stage
 constexpr int CHUNKS = (PASS_ROWS + EVAL_PAD) * (KC / 2);             // 16-byte copies per stage
-static_assert(M_ROWS <= 2 * PASS_ROWS && 2 * PASS_ROWS <= 5 * 32, "row-norm threads: two per row, warps 0-4");
+static_assert(M_ROWS <= 2 * PASS_ROWS && 4 * PASS_ROWS <= THREADS && KC % 8 == 0, "row-norm threads: four per row, warps 0-9");
 }  // namespace
 
 size_t score_smem_bytes(int) {
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
         for (int i = 0; i < MT; ++i)
 #pragma unroll
             for (int j = 0; j < 2; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-        double sq = 0.0;                                  // threads 0..159: half a row of the squared norm
+        double sq = 0.0, sq2 = 0.0;                       // threads 0..319: a quarter of a row of the squared norm
 
         for (int s = 0; s < STAGES - 1; ++s) {
             if (s < nk) load_stage(s, s);
@@ -146,13 +146,13 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
                 cp_async_commit();
             }
             const double* a_st = As + (kc % STAGES) * A_STAGE;
-            if (tid < 2 * PASS_ROWS) {
-                const double* x = a_st + (tid >> 1) * LDS + (tid & 1) * (KC / 2);
+            if (tid < 4 * PASS_ROWS) {                     // four threads per row, two independent chains each: the norm
+                const double* x = a_st + (tid >> 2) * LDS + (tid & 3) * (KC / 4);    // work must not hold warps 0-9 back
 #pragma unroll
-                for (int e = 0; e < KC / 2; e += 2) {
+                for (int e = 0; e < KC / 4; e += 2) {
                     const double2 v = *reinterpret_cast<const double2*>(x + e);
                     sq = fma(v.x, v.x, sq);
-                    sq = fma(v.y, v.y, sq);
+                    sq2 = fma(v.y, v.y, sq2);
                 }
             }
             const double* as = a_st + (wm * MT * 8 + fr) * LDS + fk;
@@ -169,9 +169,11 @@ __global__ void __launch_bounds__(THREADS, 1) score_kernel(ScoreParams prm) {
             }
         }
         cp_async_wait<0>();
-        if (tid < 2 * PASS_ROWS) {                         // warps 0-4, both halves of a row sit in adjacent lanes
+        if (tid < 4 * PASS_ROWS) {                         // warps 0-9, the four quarters of a row sit in adjacent lanes
+            sq += sq2;
             sq += __shfl_xor_sync(0xffffffffu, sq, 1);
-            if ((tid & 1) == 0) nrm_sm[row0 + (tid >> 1)] = sq;
+            sq += __shfl_xor_sync(0xffffffffu, sq, 2);
+            if ((tid & 3) == 0) nrm_sm[row0 + (tid >> 2)] = sq;
         }
         __syncthreads();
 
