@@ -44,13 +44,20 @@ struct SyrkCluster {
     int* inexact;         // set when a row is not exact in six digits: the float64 kernel redoes this cluster
     double* C;            // the cluster's Gram (u x ldc, lower triangle written)
     long ldc;
+    // rectangular product A B^T (the global X^T Y of mmd_upload) instead of a symmetric one: u_b > 0 columns with their own
+    // scales; all of them are written; out_rows (optional) scatters output row r to C row out_rows[r]
+    int u_b;
+    const double* scales_b;
+    const int* out_rows;
 };
 struct SyrkItem {
     int row_a, row_b;     // plane-0 tensor rows of the tile's rows (m0) and columns (n0)
     int up, cluster;
-    int m0, n0;           // n0 <= m0: lower-triangle tiles
+    int m0, n0;           // symmetric product: n0 <= m0 (lower-triangle tiles)
+    int up_b;             // plane stride of operand B (= up for the symmetric product)
 };
 size_t syrk_i8_smem_bytes();
+// rows of `Xt` (row pitch ldt halfs) listed by each cluster's `rows` (nullptr: rows 0..u-1) -> six digit planes and scales
 cudaError_t launch_slice_union(const __half* Xt, int ldt, const SyrkCluster* clusters_dev, int n_clusters, int max_u, int8_t* planes,
                                cudaStream_t s);
 cudaError_t launch_syrk_i8(const int8_t* planes, long plane_rows, int ldt, const SyrkItem* items_dev, int n_items,

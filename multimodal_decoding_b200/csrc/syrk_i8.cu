@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(256) slice_union_kernel(const __half* __restri
     const SyrkCluster cl = clusters[blockIdx.y];
     const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (r >= cl.u) return;
-    const __half* row = Xt + (long)cl.rows[r] * ldt;
+    const __half* row = Xt + (long)(cl.rows ? cl.rows[r] : r) * ldt;
     float m = 0.f;
     for (int j = lane * 8; j < ldt; j += 256) {
         const int4 v = *reinterpret_cast<const int4*>(row + j);
@@ -237,7 +237,7 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tm, const SyrkItem* __restric
                     __syncwarp();
                     if (lane < n_planes) tma_tile2d(dst + lane * PLANE, &tm, full_bar(slot), kb * KB, item.row_a + lane * item.up);
                     else if (!diag && lane >= 8 && lane < 8 + n_planes)
-                        tma_tile2d(dst + (S + lane - 8) * PLANE, &tm, full_bar(slot), kb * KB, item.row_b + (lane - 8) * item.up);
+                        tma_tile2d(dst + (S + lane - 8) * PLANE, &tm, full_bar(slot), kb * KB, item.row_b + (lane - 8) * item.up_b);
                 }
             }
         }
@@ -327,9 +327,12 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tm, const SyrkItem* __restric
             const int gr = item.m0 + row;
             if (gr < cl.u) {
                 const double sr = cl.scales[gr];
-                double* out = cl.C + (long)gr * cl.ldc + item.n0 + cg * EPI_COLS;
-                const double* sc = cl.scales + item.n0 + cg * EPI_COLS;
-                const int n_valid = min(EPI_COLS, min(cl.u, gr + 1) - (item.n0 + cg * EPI_COLS));    // lower triangle: columns <= row
+                const int col0 = item.n0 + cg * EPI_COLS;
+                const long orow = cl.out_rows ? (long)cl.out_rows[gr] : (long)gr;
+                double* out = cl.C + orow * cl.ldc + col0;
+                const double* sc = (cl.u_b > 0 ? cl.scales_b : cl.scales) + col0;
+                // symmetric product: lower triangle (columns <= row); rectangular product: all u_b columns
+                const int n_valid = min(EPI_COLS, (cl.u_b > 0 ? cl.u_b : min(cl.u, gr + 1)) - col0);
 #pragma unroll
                 for (int c = 0; c < EPI_COLS; ++c)
                     if (c < n_valid) out[c] = racc[c] * sr * sc[c];

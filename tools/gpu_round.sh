@@ -21,6 +21,7 @@ timeout 900 ncu --set full --clock-control none --import-source on -k factor_sol
      python bench.py $SMALL > gpurun_out/ncu_factor_solve_core.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k factor_solve_kernel -s 1 -c 1 -f -o gpurun_out/factor_solve_kernel \
      python bench.py $SMALL > gpurun_out/ncu_factor_solve_kernel.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_nt -s 1 -c 1 -f -o gpurun_out/gemm_syrk \
-     python bench.py $SMALL > gpurun_out/ncu_gemm.log 2>&1
+# the cluster SYRK: launch 0 of syrk_i8_kernel is the X^T Y of the upload, launch 1 the first batch's union Grams
+timeout 900 ncu --set full --clock-control none --import-source on -k syrk_i8_kernel -s 1 -c 1 -f -o gpurun_out/syrk_i8_kernel \
+     python bench.py $SMALL > gpurun_out/ncu_syrk_i8.log 2>&1
 ls -la gpurun_out
