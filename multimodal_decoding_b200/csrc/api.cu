@@ -200,6 +200,7 @@ struct mmd_handle {
     int predict_mode = 1;           // 1: tcgen05 int8 digit GEMM + float64 reroute of guarded centres; 0: float64 DMMA kernel
     int syrk_mode = 1;              // 1: exact integer cluster Gram on tcgen05 (syrk_i8.cu); 0: float64 DMMA kernel
     DevBuf syrk_planes, syrk_scales, syrk_flags, syrk_status;
+    DevBuf core_done;               // merged core + centre launch of factor_solve: per-core completion flags + the ticket
     size_t syrk_plane_rows = 0;     // rows of the current chunk's plane tensor (largest batch)
     int n_sms = 148;
     int call_batches = 0;           // batches of the current searchlight call (index into reroute_counts)
@@ -685,18 +686,11 @@ int run_batch_cv(mmd_handle* h, const SolveParams& base, const std::vector<GemmP
                 sp.gram_sub_off = (long)((cv.pool.as<double>() + (size_t)f * cv.pool_stride) - pool0);
                 span_begin(h, ST_SOLVE);
                 if (n_core > 0) {
-                    SolveParams cp = sp;
-                    cp.tasks = sp.tasks + n_tasks;
-                    cp.n_tasks = n_core;
-                    cp.kp_max = sp_max;
-                    cp.work = h->core_work.as<double>();
-                    cp.flags = h->group_flags.as<int>();
-                    cp.core_only = 1;
                     CU(cudaMemsetAsync(h->group_flags.p, 0, (size_t)n_core * sizeof(int), h->stream));
-                    CU(launch_factor_solve(cp, h->stream));
+                    CU(cudaMemsetAsync(h->core_done.p, 0, (size_t)(n_core + 1) * sizeof(int), h->stream));
                 }
-                CU(launch_factor_solve(sp, h->stream));
-                span_end(h, n_core > 0 ? 2 : 1);
+                CU(launch_factor_solve(sp, h->stream));            // cores and centres in one launch
+                span_end(h, 1);
                 span_begin(h, ST_PREDICT);
                 CU(launch_predict(pp, h->stream));
                 span_end(h);
@@ -744,6 +738,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
             const int sp = plan.grp_sp[g];
             const double* core_work = nullptr;
             const int* core_flag = nullptr;
+            const int* core_done = nullptr;
             if (sp > 0) {
                 const int t = n_tasks + q;
                 task_row_off[t] = adj_total + plan.core_off[g];
@@ -762,6 +757,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
                 ct.core_flag = nullptr;
                 core_work = h->core_work.as<double>() + (size_t)q * core_stride;
                 core_flag = h->group_flags.as<int>() + q;
+                core_done = h->core_done.as<int>() + q;
                 h->solve_flops += (double)sp * sp * sp / 3.0 + (double)EVAL_PAD * sp * sp;
                 ++q;
             }
@@ -784,6 +780,7 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
                 ct.s_p = sp;
                 ct.core_work = core_work;
                 ct.core_flag = core_flag;
+                ct.core_done = core_done;
                 const double kpd = ct.kp, spd = sp;
                 h->solve_flops += (kpd * kpd * kpd - spd * spd * spd) / 3.0 + EVAL_PAD * (kpd * kpd - spd * spd) +
                                   EVAL_PAD * kpd * kpd;
@@ -897,21 +894,29 @@ int run_batch(mmd_handle* h, const Rows& rows, const Plan& plan, int c0, int c1,
     sp.flags = h->flags.as<int>();
     sp.core_only = 0;
     sp.gram_sub_off = 0;
+    sp.n_core = n_core;
+    sp.core_tasks = sp.tasks + n_tasks;
+    sp.core_work = h->core_work.as<double>();
+    sp.core_kp_max = sp_max;
+    sp.core_flags = h->group_flags.as<int>();
+    sp.core_done = h->core_done.as<int>();
+    sp.ticket = h->core_done.as<int>() + n_core;
     if (h->cv) return run_batch_cv(h, sp, probs, n_tasks, n_core, kp, sp_max, max_u);
+    // one merged launch: the groups' shared cores (factorisation + forward solve) and the centres extending them
+    sp.n_core = n_core;
+    sp.core_tasks = sp.tasks + n_tasks;
+    sp.core_work = h->core_work.as<double>();
+    sp.core_kp_max = sp_max;
+    sp.core_flags = h->group_flags.as<int>();
+    sp.core_done = h->core_done.as<int>();
+    sp.ticket = h->core_done.as<int>() + n_core;
     span_begin(h, ST_SOLVE);
     if (n_core > 0) {
-        SolveParams cp = sp;                                   // the shared cores first: factorisation + forward solve
-        cp.tasks = sp.tasks + n_tasks;
-        cp.n_tasks = n_core;
-        cp.kp_max = sp_max;
-        cp.work = h->core_work.as<double>();
-        cp.flags = h->group_flags.as<int>();
-        cp.core_only = 1;
         CU(cudaMemsetAsync(h->group_flags.p, 0, (size_t)n_core * sizeof(int), h->stream));
-        CU(launch_factor_solve(cp, h->stream));
+        CU(cudaMemsetAsync(h->core_done.p, 0, (size_t)(n_core + 1) * sizeof(int), h->stream));
     }
     CU(launch_factor_solve(sp, h->stream));
-    span_end(h, n_core > 0 ? 2 : 1);
+    span_end(h, 1);
 
     PredictParams pp{};
     pp.tasks = sp.tasks;
@@ -1073,6 +1078,7 @@ int run_chunk(mmd_handle* h, const Rows& rows, const Plan& plan, size_t total, i
     CU(h->loc.ensure((size_t)(max_tasks + max_core) * kp * sizeof(int)));
     CU(h->core_work.ensure(std::max<size_t>((size_t)max_core * (sp_max + EVAL_PAD) * sp_max, 1) * sizeof(double)));
     CU(h->group_flags.ensure(std::max<size_t>(max_core, 1) * sizeof(int)));
+    CU(h->core_done.ensure((size_t)(max_core + 1) * sizeof(int)));
     if (with_null) CU(h->dist.ensure((size_t)max_tasks * NULL_DIST_ROWS * EVAL_PAD * sizeof(double)));
     if (h->syrk_mode == 1 && h->ldt % 64 == 0) {
         size_t max_rows = 0, max_scales = 0, max_cl = 0;
@@ -1329,7 +1335,7 @@ std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
                       &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval,
                       &h->xplanes, &h->sX, &h->colmax, &h->zplanes, &h->sZ, &h->amp2, &h->i8_status, &h->reroute_list,
                       &h->reroute_counts, &h->margins, &h->active, &h->batch_dev, &h->syrk_planes, &h->syrk_scales, &h->syrk_flags,
-                      &h->syrk_status};
+                      &h->syrk_status, &h->core_done};
 }
 
 // the stream must have passed mmd_upload's kernels (any later synchronisation of h->stream will do)

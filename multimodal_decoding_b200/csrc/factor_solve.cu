@@ -467,18 +467,39 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
     double* Ism = pipe + PIPE_DOUBLES;                          // NB x LDD: L_jj^{-1}
     __shared__ int bad_pivot;
 
-    const int task_id = blockIdx.x;
-    if (task_id >= prm.n_tasks) return;
-    const CentreTask task = prm.tasks[task_id];
+    __shared__ int ticket_sm;
+    int slot = blockIdx.x;
+    if (prm.n_core > 0) {                                       // merged launch: tickets in the order the CTAs start running
+        if (threadIdx.x == 0) ticket_sm = atomicAdd(prm.ticket, 1);
+        __syncthreads();
+        slot = ticket_sm;
+    }
+    const bool is_core = prm.core_only || slot < prm.n_core;
+    const int task_id = prm.n_core > 0 && !is_core ? slot - prm.n_core : slot;
+    if (!is_core && task_id >= prm.n_tasks) return;
+    const CentreTask task = prm.n_core > 0 && is_core ? prm.core_tasks[task_id] : prm.tasks[task_id];
+    const int kp_stride = prm.n_core > 0 && is_core ? prm.core_kp_max : prm.kp_max;
+    double* work = prm.n_core > 0 && is_core ? prm.core_work : prm.work;
+    int* flags = prm.n_core > 0 && is_core ? prm.core_flags : prm.flags;
     const int kp = task.kp, nblk = kp / NB;
     const long ld = kp;
-    double* M = prm.work + (long)task_id * (prm.kp_max + EVAL_PAD) * prm.kp_max;   // rows 0..kp-1: L ; rows kp..: W then Zt
+    double* M = work + (long)task_id * (kp_stride + EVAL_PAD) * kp_stride;   // rows 0..kp-1: L ; rows kp..: W then Zt
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double* stage = pipe + warp * 8 * LDD;
     double* Dsm = pipe;
     constexpr int N_ESTRIPS = EVAL_PAD / 16;
 
     if (tid == 0) bad_pivot = 0;
+    if (task.core_done && task.s_p > 0) {                      // merged launch: the group's core must be complete
+        if (tid == 0) {
+            int done = 0;
+            while (!done) {
+                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(done) : "l"(task.core_done) : "memory");
+                if (!done) __nanosleep(500);
+            }
+        }
+        __syncthreads();
+    }
 
     // Prefix sharing: the first jc panels of L (and of W) belong to the group's core task.
     const int s_p = task.s_p, jc = s_p / NB;
@@ -576,8 +597,13 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         __syncthreads();                                         // panel j complete (global writes visible CTA-wide)
     }
 
-    if (prm.core_only) {
-        if (tid == 0 && bad_pivot) prm.flags[task.centre] = 1;     // the caller zeroes the flags
+    if (is_core) {
+        if (tid == 0 && bad_pivot) flags[task.centre] = 1;         // the caller zeroes the flags
+        if (prm.n_core > 0) {                                      // publish: every thread's writes, then the flag
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(prm.core_done + task_id), "r"(1) : "memory");
+        }
         return;
     }
 
@@ -635,7 +661,7 @@ __global__ void __launch_bounds__(THREADS, 3) factor_solve_kernel(SolveParams pr
         __syncthreads();                                         // Zt block visible before it is read as an operand
     }
     if (tid == 0 && task.core_flag && *task.core_flag) bad_pivot = 1;
-    if (tid == 0 && bad_pivot) prm.flags[task.centre] = 1;         // zeroed by the caller; sticky over the launches of a call
+    if (tid == 0 && bad_pivot) flags[task.centre] = 1;             // zeroed by the caller; sticky over the launches of a call
 }
 
 // One 64 x 64 diagonal block of the dense blocked Cholesky (dense.cu): same in-shared-memory factorisation as above.
@@ -683,7 +709,7 @@ cudaError_t launch_factor_solve(const SolveParams& p, cudaStream_t s) {
     e = cudaFuncSetAttribute(factor_solve_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     if (e != cudaSuccess) return e;
     if (p.kp_max % NB != 0) return cudaErrorInvalidValue;
-    factor_solve_kernel<<<p.n_tasks, THREADS, smem, s>>>(p);
+    factor_solve_kernel<<<p.n_tasks + (p.n_core > 0 ? p.n_core : 0), THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 

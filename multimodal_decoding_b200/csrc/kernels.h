@@ -80,6 +80,7 @@ struct CentreTask {
     int s_p;
     const double* core_work;
     const int* core_flag;     // non-positive pivot met while factoring the shared core
+    const int* core_done;     // merged launch: set (release) by the group's core task when core_work is complete
 };
 struct SolveParams {
     const CentreTask* tasks;
@@ -90,6 +91,18 @@ struct SolveParams {
     double* work;         // per task: (task.kp + EVAL_PAD) x task.kp doubles at the start of its stride
     int* flags;           // per task slot: 1 if a non-positive pivot was met
     int core_only;        // 1: tasks are shared cores: factorisation + forward solve only (no backward solve)
+    // Merged launch (n_core > 0): ONE grid runs the groups' shared cores and the centres.  A CTA draws a ticket; tickets
+    // 0..n_core-1 are core tasks (core_tasks[t], written to core_work / core_flags, stride (core_kp_max + EVAL_PAD) *
+    // core_kp_max), the rest are the centres.  The first CTAs to run draw the lowest tickets, so a core never waits for a
+    // slot behind a centre that spins on it; a centre waits for its group's core_done flag.  The centre work fills the
+    // half-empty second wave a separate core launch leaves.
+    int n_core;
+    const CentreTask* core_tasks;
+    double* core_work;
+    int core_kp_max;
+    int* core_flags;
+    int* core_done;       // (n_core) zeroed by the caller
+    int* ticket;          // one int, zeroed by the caller
     long gram_sub_off;    // 0, or the offset (in doubles) from task.gram to a second Gram of the same layout that is subtracted:
                           // A = G[loc,loc] - G_f[loc,loc] + alpha I, the normal matrix without the trials of fold f (cv.cu)
 };
