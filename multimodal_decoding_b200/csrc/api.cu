@@ -173,7 +173,7 @@ struct mmd_handle {
     bool uploaded = false;
     DevBuf Xt, Xe, Yt, cand, cand64, cand_sq, XtY;
     // per-call / per-batch workspaces
-    DevBuf adj, union_vertices, task_row, task_k, task_core_off, task_core_n, core_work, group_flags, task_union_off, task_union_n, nbr_sorted, loc, tasks, probs, gram_pool,
+    DevBuf adj, union_vertices, core_work, group_flags, nbr_sorted, loc, probs, gram_pool,
         work, yhat, scores, flags, misc_flag, tmp;
     // null-distribution scoring (optional) and the generic eval.py primitives
     DevBuf vertex_bad, y_bad;               // per vertex: 1 = betas hold NaN/inf, 2 = outside the active set; one int: training latents hold NaN/inf
@@ -1329,7 +1329,7 @@ int report_input_flags(mmd_handle* h, int bad, int y_bad, const char* who) {
 // every device buffer the handle owns
 std::vector<DevBuf*> handle_buffers(mmd_handle* h) {
     return {&h->Xt, &h->Xe, &h->Yt, &h->cand, &h->cand64, &h->cand_sq, &h->XtY, &h->adj, &h->union_vertices,
-                      &h->task_row, &h->task_k, &h->task_core_off, &h->task_core_n, &h->core_work, &h->group_flags, &h->task_union_off, &h->task_union_n, &h->nbr_sorted, &h->loc, &h->tasks,
+                      &h->core_work, &h->group_flags, &h->nbr_sorted, &h->loc,
                       &h->probs, &h->gram_pool, &h->work, &h->yhat, &h->scores, &h->flags, &h->misc_flag, &h->tmp,
                       &h->st_in, &h->st_edges, &h->st_label, &h->st_count, &h->st_out, &h->dist, &h->null_out, &h->perm_test, &h->perm_im, &h->perm_im_centre, &h->pa_pred, &h->pa_lat, &h->pa_dist,
                       &h->pa_sq, &h->pa_count, &h->vertex_bad, &h->y_bad, &h->up_x, &h->up_y, &h->up_train, &h->up_eval,

@@ -16,10 +16,8 @@ for kn in predict_i8_kernel score_kernel; do
   timeout 900 ncu --set full --clock-control none --import-source on -k $kn -s 0 -c 1 -f -o gpurun_out/${kn} \
      python bench.py $SMALL > gpurun_out/ncu_${kn}.log 2>&1
 done
-# factor_solve runs twice per batch: the groups' shared cores (launch 0), then the per-centre launch (launch 1)
-timeout 900 ncu --set full --clock-control none --import-source on -k factor_solve_kernel -s 0 -c 1 -f -o gpurun_out/factor_solve_core \
-     python bench.py $SMALL > gpurun_out/ncu_factor_solve_core.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k factor_solve_kernel -s 1 -c 1 -f -o gpurun_out/factor_solve_kernel \
+# factor_solve: one merged launch per batch (the groups' shared cores + the centres)
+timeout 900 ncu --set full --clock-control none --import-source on -k factor_solve_kernel -s 0 -c 1 -f -o gpurun_out/factor_solve_kernel \
      python bench.py $SMALL > gpurun_out/ncu_factor_solve_kernel.log 2>&1
 # the cluster SYRK: launch 0 of syrk_i8_kernel is the X^T Y of the upload, launch 1 the first batch's union Grams
 timeout 900 ncu --set full --clock-control none --import-source on -k syrk_i8_kernel -s 1 -c 1 -f -o gpurun_out/syrk_i8_kernel \
