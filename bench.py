@@ -361,6 +361,17 @@ def roofline_entry(stats, n_centres, args, peaks):
     return out
 
 
+def workload_config(args, V, world, weak, cps):
+    """The `config` of the JSON line: the workload (BASELINE.json configs[1]) and how it is laid out over the GPUs.  Both arms
+    print the same dict (the reference arm times a bounded sample of this workload, stated in its cpu_baseline.sample)."""
+    return {"workload": WORKLOAD,
+            "n_vertices": int(V), "n_neighbors": args.n_neighbors, "n_train": args.n_train, "n_test": 140, "n_imagery": 3,
+            "n_dims": args.n_dims, "alpha": 1.0, "centres_per_step_per_gpu": int(cps),
+            "sharding": (f"{world} hemisphere job(s), one per GPU" if weak else
+                         f"one hemisphere, Morton-ordered vertex ranges x{world}, score maps all-gathered"),
+            "l2": "inputs larger than L2 (Xt 1.3 GB, per-step workspaces > 126 MB); no flush needed"}
+
+
 # ----------------------------------------------------------------------------------------------------------
 # arms
 # ----------------------------------------------------------------------------------------------------------
@@ -565,7 +576,8 @@ def run_ours(args):
     # N > 1: the headline is the north star's split -- ONE hemisphere, vertex-sharded ("strong"); the replica layout (one
     # whole hemisphere job per GPU) is measured in the same run and reported beside it
     mode = "weak" if world == 1 else args.scaling
-    m = measure(args, mode, rank, world, local, eng, with_cpu=not args.no_cpu_baseline)
+    # the CPU leg (the unmodified reference on the host cores + the live parity sample) runs at N = 1 only
+    m = measure(args, mode, rank, world, local, eng, with_cpu=not args.no_cpu_baseline and world == 1)
     replicas = None
     if world > 1 and mode == "strong" and not args.no_replicas:
         torch.cuda.empty_cache()
@@ -581,12 +593,7 @@ def run_ours(args):
             "ms_per_step": round(m["dev_s"] / K * 1e3, 3), "higher_is_better": True,
             "scaling": "weak" if (weak and world > 1) or args.scaling == "weak" else "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD,
-                       "n_vertices": V, "n_neighbors": k, "n_train": args.n_train, "n_test": 140, "n_imagery": 3,
-                       "n_dims": args.n_dims, "alpha": 1.0, "centres_per_step_per_gpu": cps,
-                       "sharding": (f"{world} hemisphere job(s), one per GPU" if weak else
-                                    f"one hemisphere, Morton-ordered vertex ranges x{world}, score maps all-gathered"),
-                       "l2": "inputs larger than L2 (Xt 1.3 GB, per-step workspaces > 126 MB); no flush needed"},
+            "config": workload_config(args, V, world, weak, cps),
             "wall_ms_per_step": round(m["wall"] / K * 1e3, 3),
             "e2e": m["e2e"], "gpu_launches": int(stats["launches"]),
             "roofline": roofline_entry(stats, cps * K, args, peaks),
@@ -616,6 +623,7 @@ def run_reference(args):
     import torch
     k, n_tr, D = args.n_neighbors, args.n_train, args.n_dims
     cores = host_cores()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     n_c = 8 * cores                                             # centres per step (bounded sample)
     n_rows = (args.warmup + args.steps) * n_c
     device = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
@@ -650,14 +658,21 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     arm.close()
     v = n_c * args.steps / dt
+    # the own arm's layout for this N (run_ours / measure): strong scaling when N > 1
+    from multimodal_decoding_b200.sharding import split_bounds
+    weak_own = world == 1 or args.scaling == "weak"
+    V_all = len(coords)
+    cps_own = V_all if weak_own else min(b - a for a, b in split_bounds(V_all, world))
+    if args.centres_per_step:
+        cps_own = min(args.centres_per_step, cps_own)
     sample = f"{n_c} consecutive centres per step x {args.steps} steps, k={k}, N_train={n_tr}, D={D}; {how}"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 2),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        # the own arm's workload; each step is a bounded sample of its centres (cpu_baseline.sample)
-        "config": {"workload": WORKLOAD, "n_vertices": int(len(coords)), "n_neighbors": k, "n_train": n_tr,
-                   "n_test": 140, "n_imagery": 3, "n_dims": D, "alpha": 1.0, "centres_per_step_sampled": n_c},
+        "higher_is_better": True, "scaling": "weak" if (weak_own and world > 1) or args.scaling == "weak" else "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        # the own arm's workload and layout; each step here is a bounded sample of its centres (cpu_baseline.sample)
+        "config": workload_config(args, len(coords), world, weak_own, cps_own),
         "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "the reference's CPU path (Python + sklearn/scipy, float64) on all host cores; inputs generated like the own "
