@@ -7,14 +7,16 @@ k = 750 nearest neighbours, N_train = 4000, 140 test + 3 imagery trials, D = 102
 modality-agnostic.  A *step* is one pass of the hot path over a whole hemisphere (all 163,842 centres; with
 `--centres-per-step` a range of that many consecutive centres).  `value` is measured with the trial arrays already
 staged in HBM (CUDA events on the engine's stream); `e2e` calls the public drop-in `custom_search_light` with HOST
-buffers every step (pinned X, y and the int64 adjacency in; the object array of score dicts out).  With N > 1
-(torchrun) every rank runs its own hemisphere job ("weak" scaling, configs[4] distributes whole searchlights; no
-data-path collective, the score blocks are all-gathered once per step); `--scaling strong` shards ONE hemisphere
-into Morton-ordered vertex ranges instead.
+buffers every step (pinned X, y and the int64 adjacency in; the object array of score dicts out).
 
-`--impl reference` times the CPU restatement of the reference's per-centre loop (oracle/, float64 numpy/scipy) run
-the way the reference runs it -- joblib processes over chunks of centres on all host cores -- on a bounded sample of
-the same workload.
+N > 1 (torchrun): the headline is the north star's split -- ONE hemisphere, its centres in Morton order, rank r scores the
+r-th contiguous range, the score blocks are all-gathered once per step ("scaling": "strong") -- and the replica layout
+(every rank runs one whole hemisphere job of its own, no data-path collective) is measured in the same run and reported in
+`replicas`.  `--scaling weak` makes the replica layout the headline.
+
+At N = 1 the line also carries `cpu_baseline` (the UNMODIFIED reference from baseline/_ref -- custom_search_light + sklearn
+Ridge -- on a contiguous sample of the same workload, all host cores) and `parity_sample` (the same centres scored on the GPU,
+compared).  `--impl reference` times that reference alone, step by step, and prints the own arm's `config`.
 """
 from __future__ import annotations
 
