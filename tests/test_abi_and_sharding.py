@@ -89,6 +89,20 @@ def test_score_dicts_helper_matches_python_construction():
         assert all(list(a.items())[:3] == list(b.items())[:3] for a, b in zip(got[:7], slow[:7]))
 
 
+def test_mark_vertices_host_helper():
+    """mmd_mark_vertices (host threads, no GPU): the vertices a shard's neighbourhoods use, as the sharded upload needs them."""
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+    rng = np.random.default_rng(5)
+    A = rng.integers(0, 5000, size=(3000, 700))                      # int64, > 1 Mi entries: several host threads
+    got = sl._active_vertices(A[:40], 5000)
+    assert np.array_equal(got, np.unique(A[:40]))
+    assert sl._active_vertices(A, 5000) is None                       # (nearly) every vertex: no subset
+    ragged = [A[0, :5].astype(np.int32), A[1, :9].astype(np.int32)]
+    assert np.array_equal(sl._active_vertices(ragged, 5000), np.unique(np.concatenate(ragged)))
+    with pytest.raises(ValueError, match="outside"):
+        sl._active_vertices(np.array([[1, 2, 5000]]), 5000)
+
+
 def test_split_bounds_equals_array_split():
     from multimodal_decoding_b200.sharding import split_bounds, spatial_order
     for n, parts in ((163842, 8), (10, 3), (7, 7), (5, 8)):
