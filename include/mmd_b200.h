@@ -199,6 +199,31 @@ int mmd_dist_mat_to_pairwise_acc(mmd_handle* h, const double* dist_mat, int n_ro
 int mmd_pairwise_accuracy(mmd_handle* h, const double* latents, int n_lat, const double* predictions, int n_pred,
                           int n_dims, int standardize_predictions, int standardize_latents, double* acc_out);
 
+/* mmd_pairwise_accuracy for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  This entry point has no counterpart in the reference.
+ * Same arithmetic and kernels as mmd_pairwise_accuracy, but
+ *   - `latents` (n_lat x n_dims), `predictions` (n_pred x n_dims) and `acc_out` (one double) are DEVICE memory of GPU
+ *     `device`, float64 row-major; nothing is staged, the inputs are not modified;
+ *   - the scratch (standardised copies, row norms, distance matrix, counter) is a file-scope `static __device__` array of
+ *     MMD_STATIC_SCRATCH_BYTES (4.5 MiB) inside the library: every GPU that loads the library holds it until the process
+ *     exits.  Limits: n_lat, n_pred <= MMD_STATIC_MAX_ROWS, n_dims <= MMD_STATIC_MAX_DIMS; larger problems are rejected
+ *     with an error (use mmd_pairwise_accuracy);
+ *   - the call makes `device` current, calls no cudaMalloc / cudaFree / allocating library routine, and does NOT
+ *     synchronise: the kernels are enqueued on `stream` (a cudaStream_t; NULL = the default stream) and `acc_out` is
+ *     valid once that stream has passed them;
+ *   - all calls on a GPU share the one array (it keeps the previous call's contents; what must start at zero is cleared
+ *     on the stream): calls that overlap on the GPU -- different streams, threads or graph launches in flight -- race
+ *     and must be serialised by the caller;
+ *   - the first call on a device resolves the array's address (cudaGetSymbolAddress) and loads the kernels: make it
+ *     outside any stream capture.
+ * No handle: on failure a non-zero code is returned and, if `err` is not NULL, a message is written to err[0..err_len). */
+#define MMD_STATIC_MAX_ROWS 256
+#define MMD_STATIC_MAX_DIMS 1024
+#define MMD_STATIC_SCRATCH_BYTES 4722944
+int mmd_pairwise_accuracy_static(int device, void* stream, const double* latents, int n_lat, const double* predictions,
+                                 int n_pred, int n_dims, int standardize_predictions, int standardize_latents,
+                                 double* acc_out, char* err, int err_len);
+
 /* Group-level statistics on the score maps the searchlight writes (HOST buffers).
  *   mmd_ttest_1samp     calc_image_t_values(data, popmean, sigma=sigma): per vertex the one-sample t-value of
  *                       `data[:, v] - popmean` over subjects, NaN where all subjects agree

@@ -15,7 +15,7 @@ EVAL_PAD = 144
 EXPORTS = [
     "mmd_create", "mmd_destroy", "mmd_last_error", "mmd_version", "mmd_score_name", "mmd_knn", "mmd_radius_neighbors", "mmd_upload", "mmd_upload_active", "mmd_mark_vertices",
     "mmd_searchlight", "mmd_searchlight_i64", "mmd_searchlight_ragged", "mmd_predict_centre", "mmd_get_stats", "mmd_get_counters", "mmd_set_group_size", "mmd_reset_stats", "mmd_stage_name", "mmd_configure", "mmd_stream",
-    "mmd_searchlight_null", "mmd_searchlight_null_pc", "mmd_searchlight_null_ragged", "mmd_searchlight_cv", "mmd_ridge_load", "mmd_ridge_cv", "mmd_ridge_fit", "mmd_ridge_predict", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy",
+    "mmd_searchlight_null", "mmd_searchlight_null_pc", "mmd_searchlight_null_ragged", "mmd_searchlight_cv", "mmd_ridge_load", "mmd_ridge_cv", "mmd_ridge_fit", "mmd_ridge_predict", "mmd_cosine_distances", "mmd_dist_mat_to_pairwise_acc", "mmd_pairwise_accuracy", "mmd_pairwise_accuracy_static",
     "mmd_ttest_1samp", "mmd_tfce", "mmd_cluster_labels", "mmd_check_guards", "mmd_guard_selftest",
     "mmd_set_predict_mode", "mmd_set_syrk_mode", "mmd_enable_margins", "mmd_get_margins",
 ]
@@ -89,6 +89,8 @@ def load():
     lib.mmd_dist_mat_to_pairwise_acc.restype = i32
     lib.mmd_pairwise_accuracy.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, C.POINTER(dbl)]
     lib.mmd_pairwise_accuracy.restype = i32
+    lib.mmd_pairwise_accuracy_static.argtypes = [i32, vp, vp, i32, vp, i32, i32, i32, i32, vp, C.c_char_p, i32]
+    lib.mmd_pairwise_accuracy_static.restype = i32
     lib.mmd_ttest_1samp.argtypes = [vp, vp, i32, i32, dbl, dbl, i32, vp]
     lib.mmd_ttest_1samp.restype = i32
     lib.mmd_tfce.argtypes = [vp, vp, i32, i32, vp, i32, dbl, dbl, dbl, vp]
