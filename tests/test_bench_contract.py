@@ -4,6 +4,7 @@ run the bench."""
 import glob
 import json
 import os
+import re
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -14,9 +15,10 @@ def _line(path):
 
 
 def _latest(pattern):
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", pattern)))
+    files = glob.glob(os.path.join(ROOT, "profiles", pattern))
     assert files, pattern
-    return files[-1]
+    # v12 comes after v9: order by the numbers in the name, not by the characters
+    return max(files, key=lambda f: [int(t) for t in re.findall(r"\d+", os.path.basename(f))])
 
 
 def test_own_arm_line_has_the_contract_keys():
