@@ -90,6 +90,53 @@ def test_score_dicts_helper_matches_python_construction():
         assert all(list(a.items())[:3] == list(b.items())[:3] for a, b in zip(got[:7], slow[:7]))
 
 
+def test_score_dicts_built_ahead_of_the_scores():
+    """_DictPrebuild: the dicts are created on a helper thread while the library call runs, the values are written when the
+    scores arrive; the result equals the plain construction, also when the scores arrive first or the call never starts."""
+    import ctypes
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+    rng = np.random.default_rng(11)
+    n = 20000
+    block = rng.random((n, 8))
+    block[3, 5] = np.nan
+    want = sl._scores_to_dicts(block)
+
+    def same(a, b):
+        return len(a) == len(b) and all(
+            list(x.keys()) == list(y.keys()) and all((u == v) or (u != u and v != v) for u, v in zip(x.values(), y.values()))
+            for x, y in zip(a, b))
+
+    pb = sl._DictPrebuild(n)
+    pb.start()
+    ctypes.CDLL(None).usleep(100000)                  # a call that releases the GIL, like the searchlight call
+    got = pb.finish(block)
+    assert got.dtype == object and got.shape == (n,) and same(got, want)
+    assert all(type(v) is float for v in got[3].values())
+    assert len({id(v) for d in got[:500] for v in d.values()}) == 4000          # no float object is shared between dicts
+    # the scores arrive before the helper thread is done
+    pb = sl._DictPrebuild(n)
+    pb.start()
+    assert same(pb.finish(block), want)
+    # start() never reached (an error before the searchlight call), a second finish, an unexpected block shape, no centres
+    pb = sl._DictPrebuild(n)
+    assert same(pb.finish(block), want)
+    pb.start()
+    pb.cancel()
+    assert pb.thread is None and same(pb.finish(block[:10]), want[:10])
+    pb = sl._DictPrebuild(n)
+    pb.start()
+    assert same(pb.finish(block[:7]), want[:7])
+    assert sl._DictPrebuild(0).finish(np.zeros((0, 8))).shape == (0,)
+    # the values of a finished array are not touched by a later call
+    first = sl._DictPrebuild(4)
+    first.start()
+    a = first.finish(block[:4])
+    second = sl._DictPrebuild(4)
+    second.start()
+    b = second.finish(block[4:8])
+    assert same(a, want[:4]) and same(b, want[4:8])
+
+
 def test_mark_vertices_host_helper():
     """mmd_mark_vertices (host threads, no GPU): the vertices a shard's neighbourhoods use, as the sharded upload needs them."""
     from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
