@@ -511,8 +511,12 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
         eng.reset_stats()
         barrier()
         t0 = time.perf_counter()
+        step_ms, call_ms = [], []
         for s in range(W, W + K):
+            t_step = time.perf_counter()
             out = e2e_step(s)
+            step_ms.append(round((time.perf_counter() - t_step) * 1e3, 1))      # includes freeing the previous result
+            call_ms.append(round(sl.LAST_TIMING.get("total", 0.0), 1))
         barrier()
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e_stats = eng.stats()
@@ -524,6 +528,7 @@ def measure(args, mode, rank, world, local, eng, with_cpu):
                "api": "custom_search_light(X_host_f16, y_host_f16, Ridge(alpha=1), A_rows, ...)",
                "host_ms_last_call_rank0": {k_: round(v_, 1) for k_, v_ in sl.LAST_TIMING.items()},
                "gpu_stage_ms_per_step_rank0": {k_: round(v_ / K, 1) for k_, v_ in e2e_stats["stage_ms"].items() if v_ > 0},
+               "step_ms_rank0": step_ms, "call_ms_rank0": call_ms,
                "plan_cache_hits": int(e2e_stats["plan_cache_hits"]),
                "host_plan_ms_per_step": round(e2e_stats["host_plan_ms"] / K, 1),
                "host_adjacency_ms_per_step": round(e2e_stats["host_adjacency_h2d_ms"] / K, 1)}
