@@ -193,3 +193,69 @@ def test_two_rank_gather_gloo(tmp_path):
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
         assert "ok" in o
+
+
+_WORKER_CSL = r"""
+import sys, time, warnings
+import numpy as np
+import torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from multimodal_decoding_b200.sharding import split_bounds
+from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+from multimodal_decoding_b200.engine import score_keys
+dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{sys.argv[2]}", rank=int(sys.argv[3]), world_size=2)
+rank = dist.get_rank()
+V, k = 1003, 9
+A = np.random.default_rng(0).integers(0, V, size=(V, k))
+expect = (A[:, :8] + 0.25 * np.arange(8)).astype(np.float64)          # a score block any rank can recompute
+calls = []
+
+def fake_scores(X, y, estimator, rows, train_ids, test_ids, imagery_ids, *, anchors=None, shard_only=False, prebuild=None):
+    # stands in for the GPU part of search_light_scores: same signature, same moment of prebuild.start()
+    calls.append((len(rows), shard_only))
+    prebuild.start()
+    time.sleep(0.05)                                                   # the library call releases the GIL
+    flags = np.zeros(len(rows), dtype=np.int32)
+    if rank == 1:
+        flags[2] = 1                                                   # one centre of rank 1 is not positive definite
+    return (np.asarray(rows)[:, :8] + 0.25 * np.arange(8)).astype(np.float64), flags
+
+sl.search_light_scores = fake_scores
+lo, hi = split_bounds(V, 2)[rank]
+with warnings.catch_warnings(record=True) as w:
+    warnings.simplefilter("always")
+    out = sl.custom_search_light(None, None, None, A, [0], [1], [2], n_jobs=2)
+assert calls == [(hi - lo, True)], calls
+assert (len(w) == 1 and str(split_bounds(V, 2)[1][0] + 2) in str(w[0].message)) if rank == 1 else len(w) == 0
+bad = split_bounds(V, 2)[1][0] + 2
+keys = list(score_keys())
+assert out.dtype == object and out.shape == (V,)
+for i in range(V):
+    assert list(out[i].keys()) == keys
+    vals = list(out[i].values())
+    if i == bad:
+        assert all(v != v for v in vals)                               # NaN on every rank, not only the one that saw the flag
+    else:
+        assert vals == list(expect[i]), (i, vals, expect[i])
+# n_jobs=1: the whole call stays on this process (no collective), every centre scored locally
+calls.clear()
+out1 = sl.custom_search_light(None, None, None, A[:50], [0], [1], [2], n_jobs=1)
+assert calls == [(50, False)] and len(out1) == 50
+dist.destroy_process_group()
+print("ok", rank)
+"""
+
+
+def test_custom_search_light_host_logic_two_ranks_gloo(tmp_path):
+    """The host side of the vertex-sharded call on two gloo ranks, the GPU part replaced by a stub: each rank scores its
+    range of `np.array_split`, the blocks are gathered, every rank returns all dicts (prepared by the helper thread during
+    the 'GPU' call), a flagged centre is NaN everywhere."""
+    script = tmp_path / "worker_csl.py"
+    script.write_text(_WORKER_CSL)
+    port = str(31500 + os.getpid() % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+        assert "ok" in o
