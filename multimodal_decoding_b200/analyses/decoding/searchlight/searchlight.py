@@ -317,6 +317,21 @@ def _active_vertices(A, n_vertices):
     return None if len(active) > 0.9 * n_vertices else active
 
 
+def _wants_active_set(A, n_vertices):
+    """Whether a shard should restrict the upload's X^T Y rows to the vertices its neighbourhoods use.  Finding them is one
+    pass of the host over the shard's adjacency (18 ms for 1/8 of a 750-neighbour hemisphere); it saves GPU time of the
+    upload (15 ms for all 163,842 vertices) that runs in the shadow of the library's own pass over the same adjacency
+    anyway.  At N = 2 the end-to-end step is 41 ms shorter without it (profiles/r2_bench_n2_v4.json -> v5) and the N = 8
+    breakdown says the same (18 ms of marking against < 12 ms of hidden kernels), so it is taken only when the shard is a
+    small part of the mesh (more than 16 ranks per hemisphere).  MMD_B200_ACTIVE=1 / 0 forces it on / off."""
+    mode = os.environ.get("MMD_B200_ACTIVE", "auto").lower()
+    if mode in ("1", "on", "yes"):
+        return True
+    if mode in ("0", "off", "no"):
+        return False
+    return len(A) * 16 < n_vertices
+
+
 def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *, device=None, is_caption=None,
                         upload=True, anchors=None, shard_only=False, prebuild=None):
     """(n_centres x 8) float64 score block and per-centre flags for the centres in `A` on one GPU.
@@ -330,7 +345,7 @@ def search_light_scores(X, y, estimator, A, train_ids, test_ids, imagery_ids, *,
             is_caption = _is_caption_mask(len(test_ids))
         # a rank of a vertex-sharded call stages the cross-covariance rows of its own neighbourhoods only
         with _Phase("active_vertices"):
-            active = _active_vertices(A, np.shape(X)[1]) if shard_only and len(A) else None
+            active = _active_vertices(A, np.shape(X)[1]) if shard_only and len(A) and _wants_active_set(A, np.shape(X)[1]) else None
         Xd = _as_f16(X, "X")
         if shard_only and isinstance(Xd, np.ndarray):
             # every rank holds the same host X: each copies 1/N of its rows over PCIe, NVLink carries the rest
