@@ -151,6 +151,18 @@ def test_mark_vertices_host_helper():
         sl._active_vertices(np.array([[1, 2, 5000]]), 5000)
 
 
+def test_active_set_is_taken_for_small_shards_only(monkeypatch):
+    from multimodal_decoding_b200.analyses.decoding.searchlight import searchlight as sl
+    monkeypatch.delenv("MMD_B200_ACTIVE", raising=False)
+    V = 163842
+    assert not sl._wants_active_set(np.empty((V // 2, 3)), V) and not sl._wants_active_set(np.empty((V // 8, 3)), V)
+    assert sl._wants_active_set(np.empty((V // 32, 3)), V)
+    monkeypatch.setenv("MMD_B200_ACTIVE", "1")
+    assert sl._wants_active_set(np.empty((V // 2, 3)), V)
+    monkeypatch.setenv("MMD_B200_ACTIVE", "0")
+    assert not sl._wants_active_set(np.empty((V // 32, 3)), V)
+
+
 def test_split_bounds_equals_array_split():
     from multimodal_decoding_b200.sharding import split_bounds, spatial_order
     for n, parts in ((163842, 8), (10, 3), (7, 7), (5, 8)):
