@@ -124,16 +124,31 @@ def search_light_cv(eng, A, alphas, n_splits, n_train):
 
 
 def _as_f16(a, name):
+    """float16 view of an input of the searchlight.  The reference casts to float16 before the loop
+    (searchlight.py:247-248) and this path stores float16; `custom_search_light` itself takes any float array
+    (searchlight.py:117-129) and sklearn would fit it at its own precision, so a float32 / float64 array is accepted
+    exactly when the cast loses nothing (every value is a float16 number, e.g. float16 data that was widened): the result
+    is then the float64-exact one for those values.  Anything else raises instead of being rounded silently."""
     if hasattr(a, "data_ptr"):                        # torch tensor (possibly already on the GPU)
         import torch
         return a if a.dtype == torch.float16 else a.to(torch.float16)
     a = np.asarray(a)
     if a.dtype == np.float16:
         return a
-    # the reference casts to float16 before the loop (searchlight.py:247-248); other float inputs to
-    # custom_search_light would be fitted at their own precision by sklearn, which this path does not offer
-    raise TypeError(f"{name} must be float16 like the arrays searchlight.run builds (searchlight.py:247-248); "
-                    f"got {a.dtype}")
+    if a.dtype in (np.float32, np.float64) and a.ndim == 2:
+        out = np.empty(a.shape, dtype=np.float16)
+        step = max(1, (1 << 24) // max(1, a.shape[1]))            # ~16 Mi values per block: the temporaries stay small
+        with np.errstate(over="ignore", invalid="ignore"):
+            for r in range(0, a.shape[0], step):
+                blk = a[r:r + step]
+                out[r:r + step] = blk
+                if not np.array_equal(out[r:r + step].astype(a.dtype), blk, equal_nan=True):
+                    raise TypeError(f"{name} is {a.dtype} and holds values that are not float16 numbers: this path computes on "
+                                    f"float16 data like the arrays searchlight.run builds (searchlight.py:247-248); cast it "
+                                    f"explicitly (X.astype(np.float16)) if that rounding is intended")
+        return out
+    raise TypeError(f"{name} must be float16 like the arrays searchlight.run builds (searchlight.py:247-248), or float32 / "
+                    f"float64 holding float16 values; got {a.dtype}")
 
 
 def _is_caption_mask(n_test):

@@ -51,8 +51,21 @@ def test_estimator_protocol_and_score_dicts():
                 Ridge(alpha=np.ones(4), fit_intercept=False), object()):
         with pytest.raises(ValueError):
             sl._estimator_alpha(bad)
+    # float32 / float64 inputs are taken when the cast to float16 loses nothing, refused otherwise (never rounded silently)
+    exact = np.random.default_rng(2).standard_normal((37, 50)).astype(np.float16)
+    exact[3, 4] = np.nan
+    for wide in (np.float32, np.float64):
+        got = sl._as_f16(exact.astype(wide), "X")
+        assert got.dtype == np.float16 and np.array_equal(got, exact, equal_nan=True)
+        lossy = exact.astype(wide)
+        lossy[30, 7] = 0.1                                         # not a float16 number
+        with pytest.raises(TypeError, match="float16"):
+            sl._as_f16(lossy, "X")
+        with pytest.raises(TypeError, match="float16"):
+            sl._as_f16(np.full((2, 2), 1e6, dtype=wide), "X")      # overflows float16
     with pytest.raises(TypeError, match="float16"):
-        sl._as_f16(np.zeros((3, 3), dtype=np.float32), "X")
+        sl._as_f16(np.zeros((3, 3), dtype=np.int32), "X")
+    assert sl._as_f16(exact, "X") is exact
     block = np.random.default_rng(0).random((5, 8))
     out = sl._scores_to_dicts(block)
     assert out.shape == (5,) and out.dtype == object
